@@ -1,0 +1,42 @@
+// comm.hpp — multi-GPU plumbing: one process per GPU, paths sharded across ranks.  The only exchanges on
+// the path are (1) the double-double Gram partials of the pre-pass, (2) one gather of G'xK regression sums per backward
+// step and (3) the final per-period / NPV sums.  All of them are all-gathers followed by a sum in rank order, so every
+// rank computes bit-identical regression coefficients.  NCCL is loaded with dlopen the first time a communicator is
+// requested: the library itself has no link-time dependency on it and single-GPU runs never touch it.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+namespace lsmc {
+
+class Comm {
+ public:
+  Comm() = default;
+  ~Comm();
+  Comm(const Comm &) = delete;
+  Comm &operator=(const Comm &) = delete;
+
+  static void unique_id(void *id_out);  // rank 0: LSMC_COMM_ID_BYTES bytes to broadcast to the other ranks
+  void init(const void *id, int rank, int world, int64_t total_sims);
+
+  int world() const { return world_; }
+  int rank() const { return rank_; }
+  int64_t total_sims(int64_t local) const { return world_ > 1 ? total_sims_ : local; }
+
+  // recv[r][count] <- rank r's send[count] (device pointers), on `stream`
+  void all_gather(const double *send, double *recv, size_t count, cudaStream_t stream);
+  // sums n host doubles over ranks in rank order (no-op for a single rank); synchronises `stream`
+  void all_reduce_host(double *values, size_t n, cudaStream_t stream);
+
+ private:
+  int world_ = 1, rank_ = 0;
+  int64_t total_sims_ = 0;
+  void *nccl_comm_ = nullptr;
+  double *d_send_ = nullptr, *d_recv_ = nullptr;
+  size_t staging_ = 0;
+  void ensure_staging(size_t count);
+};
+
+}  // namespace lsmc

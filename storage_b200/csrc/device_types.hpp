@@ -1,0 +1,100 @@
+// device_types.hpp — plain structs shared by the host orchestration (lsmc_api.cu) and the kernels (kernels.cu).
+#pragma once
+#include <cstdint>
+
+#include "../../include/lsmc_b200.h"
+
+namespace lsmc {
+
+constexpr int kThreads = 128;            // threads per CTA in the path-parallel kernels
+constexpr int kPathsPerThread = 2;       // double2 vectorisation over adjacent paths
+constexpr int kTilePaths = kThreads * kPathsPerThread;
+constexpr int kWarps = kThreads / 32;
+constexpr int kAccK = 8;                 // regression partial sums are stored padded to 8 (or 16) per grid point
+constexpr int kMaxGridTile = 32;         // inventory-grid points per CTA in the backward kernel
+
+// Device copy of host_model.hpp's DecisionEntry (same layout).
+struct DevDecision {
+  double volume, cost_npv, consumed, lower_w, upper_w;
+  int32_t lower, upper;
+};
+
+// How the orthonormalised basis row q[0..K) of one path is obtained for one period.
+struct BasisSpec {
+  const double *spot;                    // [N] spot prices of the period (NULL in mean mode)
+  const double *factors[LSMC_MAX_FACTORS];  // [N] each
+  const double *rinv;                    // [K*K*2] upper-triangular R^-1 as (hi,lo) pairs, row-major [l][j]
+  int mean_mode;                         // 1: q = e_0 (current-period step: continuation value = sample mean)
+};
+
+struct BackwardStepArgs {
+  int64_t N;            // paths on this device
+  int64_t pitch;        // row pitch of the V buffers, in doubles
+  int G;                // grid points of this period
+  int Gn;               // grid points of the next period
+  int D;                // max decisions (row width of the decision table)
+  int K;                // basis functions
+  int F;                // factors
+  const double *v_next; // [Gn][pitch]
+  double *v_this;       // [G][pitch]
+  const double *gamma;  // [Gn][K] regression coefficients (orthonormal basis) of v_next on this period's basis
+  const DevDecision *decisions;  // [G][D]
+  const int32_t *num_decisions;  // [G]
+  const double *inventory_cost;  // [G]
+  const double *spot;   // [N] prices used for the immediate cash flow (NULL: use const_price)
+  double const_price;   // forward price when the period is the current period
+  double settle_df;
+  BasisSpec basis_this; // basis evaluating the continuation value of this period
+  BasisSpec basis_prev; // basis of period-1, against which v_this is accumulated (regression of the next backward step)
+  int accumulate;       // 0: no further regression (period 0)
+  double *partials;     // [num_chunks][G][accK] per-chunk sums of q_prev[k] * v_this[g]
+  int acc_k;            // kAccK or 16
+  int tiles_per_chunk;  // path tiles a CTA walks through
+  const int32_t *powers;  // [K][1+F]
+  // terminal mode: v_this[g][n] = TerminalStorageNpv(spot[n], grid_this[g]) instead of the decision step
+  int terminal_mode;
+  const double *grid_this;  // [G]
+  double terminal[4];
+};
+
+// Per-period storage parameters for the forward pass (device-evaluable ICmdtyStorage).
+struct DevPeriodParams {
+  double min_inventory, max_inventory;
+  double inj_cost, inj_df, wd_cost, wd_df, cons_inj, cons_wd, loss, inv_cost, inv_cost_df;
+  double next_space_lo, next_space_hi;
+  double settle_df, forward_price, delta_df;
+  int32_t kind, rbegin, rcount, poly_begin;
+  int32_t grid_next_count;   // points in the next period's grid
+  int32_t mean_mode;         // period 0 when the current period is active
+  int32_t sim_row;           // row of this period in the simulation panels (-1: not simulated)
+  int32_t pad;
+};
+
+constexpr int kForwardSums = 8;  // sum_spot_vol, sum_vol, sum_cons, sum_loss, sum_pv, sum_inventory (+2 spare) then K basis sums
+
+struct ForwardArgs {
+  int64_t N;
+  int P, K, F, Gmax;
+  int64_t sim_pitch;               // N (caller layout)
+  const DevPeriodParams *periods;  // [P]
+  const double *ratchet_inventory, *ratchet_min, *ratchet_max;
+  const double *poly_min, *poly_max;
+  const double *grids;             // [P+1][Gmax]
+  const double *gamma;             // [P][Gmax][K]
+  const double *rinv;              // [P][K*K*2]
+  const int32_t *powers;           // [K][1+F]
+  const double *spot;              // valuation sims [rows][N]
+  const double *factors[LSMC_MAX_FACTORS];
+  double start_inventory;
+  double tolerance;
+  int extra_decisions;
+  double *pv_by_sim;               // [N]
+  double *final_inventory;         // [N]
+  double *step_sums;               // [P][num_ctas][kForwardSums + K]
+  int sums_width;
+  // optional panels [P+1][N] (NULL = not requested)
+  double *p_inventory, *p_volume, *p_consumed, *p_loss, *p_net_volume, *p_pv, *p_decision;
+  int32_t *error_flag;             // set to an lsmc_status when a path leaves the feasible region
+};
+
+}  // namespace lsmc

@@ -1,0 +1,827 @@
+// kernels.cu — hand-written sm_100a kernels of the LSMC hot path.
+//
+//   gram_kernel / cholesky_kernel   regression pre-pass: double-double Gram matrix of the monomial design matrix of every
+//                                   period (LSV.cs:838-855 PopulateDesignMatrix), its Cholesky factor R and R^-1, i.e. the
+//                                   thin-QR of LSV.cs:193-196 formed without ever materialising Q.
+//   backward_step_kernel            one backward-induction step (LSV.cs:240-338) for a (path tile x inventory-grid tile):
+//                                   continuation value = q(path) . gamma(grid point), decision argmax, storage value;
+//                                   fused with the accumulation of q_prev^T V for the regression of the next backward
+//                                   step, so every storage value is written once and read once.
+//   reduce_partials_kernel          fixed-order reduction of the per-chunk regression partial sums -> gamma (LSV.cs:204).
+//   forward_kernel                  the whole forward simulation (LSV.cs:390-521) in one launch: a thread carries its path
+//                                   through all periods; per-period sums are reduced per CTA in a fixed order.
+//   sum kernels                     deterministic reductions for NPV / standard error / backward NPV.
+//
+// HBM-bound FP64 streaming work: no tensor cores.  Paths are the contiguous dimension of every buffer so
+// warps read and write whole 128-byte lines; the storage-value slabs use a 256-byte row pitch and are stored as double2.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "dd.cuh"
+#include "device_types.hpp"
+#include "kernels.hpp"
+
+namespace lsmc {
+
+namespace {
+
+constexpr unsigned kFullMask = 0xffffffffu;
+
+// ------------------------------------------------------------------------------------------------------------------
+// Orthonormalised basis row of one path: monomials X_k (BasisFunctions.Generic, BasisFunctions.cs:93-135; integer powers
+// correctly rounded, products in factor-index order) followed by q_j = sum_{l<=j} X_l * Rinv[l][j] in double-double.
+// ------------------------------------------------------------------------------------------------------------------
+template <int KP>
+__device__ __forceinline__ void eval_monomials(const BasisSpec &b, const int32_t *__restrict__ pw, int K, int F, int64_t n,
+                                               double (&X)[KP]) {
+  const double s = b.spot[n];
+  double x[LSMC_MAX_FACTORS];
+#pragma unroll
+  for (int i = 0; i < LSMC_MAX_FACTORS; ++i) x[i] = (i < F) ? b.factors[i][n] : 0.0;
+#pragma unroll
+  for (int k = 0; k < KP; ++k) {
+    double m = 1.0;
+    if (k < K) {
+      const int32_t *row = pw + k * (1 + F);
+      const int p0 = row[0];
+      if (p0 > 0) m = pow_int_rounded(s, p0);
+#pragma unroll
+      for (int i = 0; i < LSMC_MAX_FACTORS; ++i) {
+        if (i < F) {
+          const int pi = row[1 + i];
+          if (pi > 0) m = m * pow_int_rounded(x[i], pi);
+        }
+      }
+    }
+    X[k] = m;
+  }
+}
+
+template <int KP>
+__device__ __forceinline__ void eval_q(const BasisSpec &b, const int32_t *__restrict__ pw, const dd *__restrict__ rinv, int K,
+                                       int F, int64_t n, bool valid, double (&q)[KP]) {
+#pragma unroll
+  for (int k = 0; k < KP; ++k) q[k] = 0.0;
+  if (!valid) return;
+  if (b.mean_mode) {
+    q[0] = 1.0;
+    return;
+  }
+  double X[KP];
+  eval_monomials<KP>(b, pw, K, F, n, X);
+#pragma unroll
+  for (int j = 0; j < KP; ++j) {
+    if (j < K) {
+      dd acc{0.0, 0.0};
+#pragma unroll
+      for (int l = 0; l <= j; ++l) acc = dd_add(acc, dd_mul_d(rinv[l * K + j], X[l]));
+      q[j] = acc.hi;
+    }
+  }
+}
+
+// Sum of 8 per-lane values over the warp with 9 shuffles: after the call every lane holds the warp total of component
+// kidx = 4*bit4(lane) + 2*bit3(lane) + bit2(lane).  The pairing order is fixed, so results are reproducible.
+__device__ __forceinline__ double warp_reduce8(const double (&v)[8], int lane, int &kidx) {
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+  double w[4], u[2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    double send = b4 ? v[i] : v[i + 4];
+    double keep = b4 ? v[i + 4] : v[i];
+    w[i] = keep + __shfl_xor_sync(kFullMask, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    double send = b3 ? w[i] : w[i + 2];
+    double keep = b3 ? w[i + 2] : w[i];
+    u[i] = keep + __shfl_xor_sync(kFullMask, send, 8);
+  }
+  double send = b2 ? u[0] : u[1];
+  double keep = b2 ? u[1] : u[0];
+  double t = keep + __shfl_xor_sync(kFullMask, send, 4);
+  t += __shfl_xor_sync(kFullMask, t, 2);
+  t += __shfl_xor_sync(kFullMask, t, 1);
+  kidx = (b4 ? 4 : 0) + (b3 ? 2 : 0) + (b2 ? 1 : 0);
+  return t;
+}
+
+__device__ __forceinline__ dd warp_reduce_dd(dd v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    dd o;
+    o.hi = __shfl_xor_sync(kFullMask, v.hi, off);
+    o.lo = __shfl_xor_sync(kFullMask, v.lo, off);
+    v = dd_add(v, o);
+  }
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Regression pre-pass
+// ------------------------------------------------------------------------------------------------------------------
+// grid = (chunks, periods); each CTA accumulates the upper triangle of X^T X over its path chunk in double-double.
+template <int KP>
+__global__ void __launch_bounds__(kThreads) gram_kernel(GramArgs a) {
+  constexpr int NP = KP * (KP + 1) / 2;
+  __shared__ int32_t s_pw[LSMC_MAX_BASIS * (1 + LSMC_MAX_FACTORS)];
+  __shared__ dd s_red[kWarps][NP];
+  const int slot = blockIdx.y;
+  const BasisSpec b = a.specs[slot];
+  const int K = a.K, F = a.F;
+  for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
+  __syncthreads();
+  dd acc[NP];
+#pragma unroll
+  for (int i = 0; i < NP; ++i) acc[i] = dd{0.0, 0.0};
+  const int64_t begin = (int64_t)blockIdx.x * a.chunk_paths;
+  const int64_t end = min(begin + a.chunk_paths, a.N);
+  for (int64_t n = begin + threadIdx.x; n < end; n += blockDim.x) {
+    double X[KP];
+    eval_monomials<KP>(b, s_pw, K, F, n, X);
+    int idx = 0;
+#pragma unroll
+    for (int i = 0; i < KP; ++i)
+#pragma unroll
+      for (int j = i; j < KP; ++j, ++idx)
+        if (j < K) acc[idx] = dd_add(acc[idx], two_prod(X[i], X[j]));
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < NP; ++i) {
+    dd r = warp_reduce_dd(acc[i]);
+    if (lane == 0) s_red[warp][i] = r;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < NP; i += blockDim.x) {
+    dd r = s_red[0][i];
+    for (int w = 1; w < kWarps; ++w) r = dd_add(r, s_red[w][i]);
+    double *dst = a.partials + (((size_t)slot * gridDim.x + blockIdx.x) * NP + i) * 2;
+    dst[0] = r.hi;
+    dst[1] = r.lo;
+  }
+}
+
+// One CTA per regression period: fixed-order sum of the chunk partials (and, when sharded, of the other ranks' sums that
+// the host gathered into `partials`), Cholesky A = R^T R and R^-1, all in double-double.  Writes rinv[slot][K*K] as
+// (hi,lo) pairs, row-major [l][j], zero below the diagonal.
+template <int KP>
+__global__ void cholesky_kernel(CholeskyArgs a) {
+  constexpr int NP = KP * (KP + 1) / 2;
+  __shared__ dd s_gram[NP];
+  const int slot = blockIdx.x;
+  const int K = a.K;
+  for (int i = threadIdx.x; i < NP; i += blockDim.x) {
+    dd r{0.0, 0.0};
+    for (int rk = 0; rk < a.num_ranks; ++rk)
+      for (int c = 0; c < a.num_chunks; ++c) {
+        const double *src = a.partials + ((((size_t)rk * a.num_slots + slot) * a.num_chunks + c) * NP + i) * 2;
+        r = dd_add(r, dd{src[0], src[1]});
+      }
+    s_gram[i] = r;
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  dd R[KP][KP], Rinv[KP][KP];
+  auto gram = [&](int i, int j) {  // i <= j, packed upper triangle of a KP x KP matrix
+    return s_gram[i * KP - i * (i - 1) / 2 + (j - i)];
+  };
+  bool ok = true;
+  for (int j = 0; j < K; ++j) {
+    for (int i = 0; i <= j; ++i) {
+      dd sum = gram(i, j);
+      for (int l = 0; l < i; ++l) sum = dd_sub(sum, dd_mul(R[l][i], R[l][j]));
+      if (i == j) {
+        if (!(sum.hi > 0.0)) {
+          ok = false;
+          sum = dd{1.0, 0.0};
+        }
+        R[i][j] = dd_sqrt(sum);
+      } else {
+        R[i][j] = dd_div(sum, R[i][i]);
+      }
+    }
+  }
+  // a pivot that lost all its digits means the monomials are linearly dependent on the simulated paths
+  for (int j = 0; j < K; ++j) {
+    dd diag = gram(j, j);
+    double rel = (R[j][j].hi * R[j][j].hi) / diag.hi;
+    if (!(rel > 1e-24)) ok = false;
+  }
+  if (!ok) atomicExch(a.error_flag, (int)LSMC_ERR_NUMERICAL);
+  for (int j = 0; j < K; ++j)
+    for (int i = j; i >= 0; --i) {
+      dd sum = (i == j) ? dd{1.0, 0.0} : dd{0.0, 0.0};
+      for (int l = i + 1; l <= j; ++l) sum = dd_sub(sum, dd_mul(R[i][l], Rinv[l][j]));
+      Rinv[i][j] = dd_div(sum, R[i][i]);
+    }
+  double *out = a.rinv + (size_t)slot * K * K * 2;
+  for (int l = 0; l < K; ++l)
+    for (int j = 0; j < K; ++j) {
+      dd v = (l <= j) ? Rinv[l][j] : dd{0.0, 0.0};
+      out[(l * K + j) * 2] = v.hi;
+      out[(l * K + j) * 2 + 1] = v.lo;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Backward induction step
+// ------------------------------------------------------------------------------------------------------------------
+struct BackwardSmem {
+  // carved from dynamic shared memory by the kernel; sizes depend on D, K, acc_k
+  DevDecision *dec;     // [TG][D]
+  double *coef;         // [TG][D][KP]
+  double *inv_cost;     // [TG]
+  int32_t *nd;          // [TG]
+  dd *rinv_this;        // [K*K]
+  dd *rinv_prev;        // [K*K]
+  int32_t *pw;          // [K*(1+F)]
+  double *acc;          // [kWarps][TG][acc_k]
+};
+
+template <int KP>
+__device__ __forceinline__ BackwardSmem carve_backward_smem(unsigned char *base, int D, int K, int F, int acc_k) {
+  BackwardSmem s;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    unsigned char *p = base + off;
+    off += (bytes + 15) & ~size_t(15);
+    return p;
+  };
+  s.dec = reinterpret_cast<DevDecision *>(take(sizeof(DevDecision) * kMaxGridTile * D));
+  s.coef = reinterpret_cast<double *>(take(sizeof(double) * kMaxGridTile * D * KP));
+  s.inv_cost = reinterpret_cast<double *>(take(sizeof(double) * kMaxGridTile));
+  s.nd = reinterpret_cast<int32_t *>(take(sizeof(int32_t) * kMaxGridTile));
+  s.rinv_this = reinterpret_cast<dd *>(take(sizeof(dd) * K * K));
+  s.rinv_prev = reinterpret_cast<dd *>(take(sizeof(dd) * K * K));
+  s.pw = reinterpret_cast<int32_t *>(take(sizeof(int32_t) * K * (1 + F)));
+  s.acc = reinterpret_cast<double *>(take(sizeof(double) * kWarps * kMaxGridTile * acc_k));
+  return s;
+}
+
+// grid = (grid tiles, path chunks): grid tiles of one path chunk are adjacent in launch order, so the halo rows of
+// v_next that neighbouring tiles share are re-read from L2, not HBM.
+template <int KP>
+__global__ void __launch_bounds__(kThreads) backward_step_kernel(BackwardStepArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int ACC = KP <= 8 ? 8 : 16;  // width of a stored partial-sum row
+  const int K = a.K, F = a.F, D = a.D, acc_k = ACC;
+  BackwardSmem s = carve_backward_smem<KP>(smem_raw, D, K, F, acc_k);
+  const int g0 = blockIdx.x * kMaxGridTile;
+  const int gcount = min(kMaxGridTile, a.G - g0);
+  const int chunk = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  // ---- prologue: stage this tile's sim-independent tables; fold the next-grid interpolation into the coefficients
+  for (int i = threadIdx.x; i < gcount * D; i += blockDim.x) {
+    const int g = i / D, d = i - g * D;
+    DevDecision e = a.decisions[(size_t)(g0 + g) * D + d];
+    s.dec[i] = e;
+    double *c = s.coef + (size_t)i * KP;
+    if (!a.terminal_mode) {
+      const double *gl = a.gamma + (size_t)e.lower * K, *gu = a.gamma + (size_t)e.upper * K;
+#pragma unroll
+      for (int k = 0; k < KP; ++k) c[k] = (k < K) ? (e.lower == e.upper ? gl[k] : gu[k] * e.upper_w + gl[k] * e.lower_w) : 0.0;
+    }
+  }
+  for (int i = threadIdx.x; i < gcount; i += blockDim.x) {
+    s.inv_cost[i] = a.inventory_cost ? a.inventory_cost[g0 + i] : 0.0;
+    s.nd[i] = a.num_decisions ? a.num_decisions[g0 + i] : 0;
+  }
+  for (int i = threadIdx.x; i < K * K; i += blockDim.x) {
+    if (a.basis_this.rinv) s.rinv_this[i] = dd{a.basis_this.rinv[2 * i], a.basis_this.rinv[2 * i + 1]};
+    if (a.accumulate && a.basis_prev.rinv) s.rinv_prev[i] = dd{a.basis_prev.rinv[2 * i], a.basis_prev.rinv[2 * i + 1]};
+  }
+  for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s.pw[i] = a.powers[i];
+  for (int i = threadIdx.x; i < kWarps * kMaxGridTile * acc_k; i += blockDim.x) s.acc[i] = 0.0;
+  __syncthreads();
+
+  const double df = a.settle_df;
+  for (int tile = 0; tile < a.tiles_per_chunk; ++tile) {
+    const int64_t n0 = ((int64_t)chunk * a.tiles_per_chunk + tile) * kTilePaths + (int64_t)threadIdx.x * kPathsPerThread;
+    if (n0 - threadIdx.x * kPathsPerThread >= a.N) break;  // whole tile is past the end (uniform across the CTA)
+    bool valid[2] = {n0 < a.N, n0 + 1 < a.N};
+    int64_t nn[2] = {valid[0] ? n0 : a.N - 1, valid[1] ? n0 + 1 : a.N - 1};  // clamped: loads stay in bounds
+
+    double q[2][KP], qp[2][KP], price[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      if (a.terminal_mode) {
+#pragma unroll
+        for (int k = 0; k < KP; ++k) q[j][k] = 0.0;
+        price[j] = a.spot[nn[j]];
+      } else {
+        eval_q<KP>(a.basis_this, s.pw, s.rinv_this, K, F, nn[j], valid[j], q[j]);
+        price[j] = a.spot ? a.spot[nn[j]] : a.const_price;
+      }
+      if (a.accumulate) {
+        eval_q<KP>(a.basis_prev, s.pw, s.rinv_prev, K, F, nn[j], valid[j], qp[j]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < KP; ++k) qp[j][k] = 0.0;
+      }
+    }
+
+    for (int g = 0; g < gcount; ++g) {
+      double v[2];
+      if (a.terminal_mode) {
+        // V_T[g][n] = TerminalStorageNpv(S_T[n], grid_T[g]) (LSV.cs:121-131)
+        const double inv = a.grid_this[g0 + g];
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+          v[j] = ((a.terminal[3] * (price[j] * inv) + a.terminal[1] * price[j]) + a.terminal[2] * inv) + a.terminal[0];
+      } else {
+        const int nd = s.nd[g];
+        const double inv_cost = s.inv_cost[g];
+        const DevDecision *dec = s.dec + (size_t)g * D;
+        const double *coef = s.coef + (size_t)g * D * KP;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          double best = 0.0, best_c = 0.0;
+          int best_d = 0;
+          for (int d = 0; d < nd; ++d) {
+            const DevDecision &e = dec[d];
+            const double *c = coef + (size_t)d * KP;
+            double cont = q[j][0] * c[0];
+#pragma unroll
+            for (int k = 1; k < KP; ++k) cont = __fma_rn(q[j][k], c[k], cont);
+            // LSV.cs:317-325, same association
+            const double inject_withdraw_npv = (-e.volume * price[j]) * df;
+            const double consumed_npv = (-e.consumed * price[j]) * df;
+            const double immediate = (inject_withdraw_npv - e.cost_npv) + consumed_npv;
+            const double total = (immediate + cont) - inv_cost;
+            if (d == 0 || total > best) {  // strict >: first maximum wins (SH.cs:206-221)
+              best = total;
+              best_c = cont;
+              best_d = d;
+            }
+          }
+          const DevDecision &e = dec[best_d];
+          const double lo = a.v_next[(size_t)e.lower * a.pitch + nn[j]];
+          double actual = lo;
+          if (e.upper != e.lower) {
+            const double up = a.v_next[(size_t)e.upper * a.pitch + nn[j]];
+            actual = up * e.upper_w + lo * e.lower_w;  // WeightedAverage (LSV.cs:828-836)
+          }
+          v[j] = best + (-best_c + actual);  // LSV.cs:330-335
+        }
+      }
+      if (!valid[0]) v[0] = 0.0;
+      if (!valid[1]) v[1] = 0.0;
+      if (valid[0]) *reinterpret_cast<double2 *>(a.v_this + (size_t)(g0 + g) * a.pitch + n0) = make_double2(v[0], v[1]);
+
+      if (a.accumulate) {
+        // q_prev^T V for the regression of the next backward step, reduced over the warp in a fixed order
+#pragma unroll
+        for (int half = 0; half < ACC; half += 8) {
+          double part[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            part[k] = 0.0;
+          }
+#pragma unroll
+          for (int k = 0; k < KP; ++k) {
+            if (k >= half && k < half + 8) part[k - half] = __fma_rn(qp[1][k], v[1], qp[0][k] * v[0]);
+          }
+          int kidx;
+          double total = warp_reduce8(part, lane, kidx);
+          if ((lane & 3) == 0) s.acc[((size_t)warp * kMaxGridTile + g) * acc_k + half + kidx] += total;
+        }
+      }
+    }
+  }
+
+  if (a.accumulate) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < gcount * acc_k; i += blockDim.x) {
+      const int g = i / acc_k, k = i - g * acc_k;
+      double sum = s.acc[((size_t)0 * kMaxGridTile + g) * acc_k + k];
+      for (int w = 1; w < kWarps; ++w) sum += s.acc[((size_t)w * kMaxGridTile + g) * acc_k + k];
+      a.partials[((size_t)chunk * a.G + g0 + g) * acc_k + k] = sum;
+    }
+  }
+}
+
+// gamma[g][k] = sum over chunks of partials[chunk][g][k], in a fixed order; one CTA per grid point.
+// mean_mode: gamma[g][0] = sum / total_paths (the sample mean of LSV.cs:181), the other components are zero.
+__global__ void reduce_partials_kernel(ReduceArgs a) {
+  const int g = blockIdx.x;
+  const int k = threadIdx.x % a.acc_k;
+  const int lane_c = threadIdx.x / a.acc_k;  // which residue class of chunks this thread sums
+  const int stride = blockDim.x / a.acc_k;
+  double sum = 0.0;
+  for (int c = lane_c; c < a.num_chunks; c += stride) sum += a.partials[((size_t)c * a.G + g) * a.acc_k + k];
+  // combine the residue classes in order
+  __shared__ double s_all[256];
+  s_all[threadIdx.x] = sum;
+  __syncthreads();
+  if (threadIdx.x < a.acc_k) {
+    double total = 0.0;
+    for (int c = 0; c < stride; ++c) total += s_all[c * a.acc_k + threadIdx.x];
+    if (threadIdx.x < a.K) {
+      double out = total;
+      if (a.mean_mode) out = (threadIdx.x == 0) ? total / (double)a.total_paths : 0.0;
+      a.out[(size_t)g * a.K + threadIdx.x] = out;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Forward simulation
+// ------------------------------------------------------------------------------------------------------------------
+struct DevRange {
+  double lo, hi;
+};
+
+__device__ __forceinline__ int left_segment_dev(const double *x, int n, double t) {
+  int lo = 0, hi = n;  // first index with x[idx] > t
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (x[mid] > t)
+      hi = mid;
+    else
+      lo = mid + 1;
+  }
+  return lo - 1;  // last knot <= t (-1 if none)
+}
+
+__device__ __forceinline__ double spline_dev(const double *x, const double *y, int n, double t) {
+  int k = left_segment_dev(x, n, t);
+  k = max(0, min(k, n - 2));
+  const double slope = (y[k + 1] - y[k]) / (x[k + 1] - x[k]);
+  return y[k] + (t - x[k]) * slope;
+}
+
+__device__ __forceinline__ double horner_dev(const double *c, int len, double z) {
+  double acc = c[len - 1];
+  for (int i = len - 2; i >= 0; --i) {
+    acc *= z;
+    acc += c[i];
+  }
+  return acc;
+}
+
+// CmdtyStorage.GetInjectWithdrawRange (CS.cs:86-100) at a per-path inventory
+__device__ __forceinline__ DevRange storage_range_dev(const ForwardArgs &a, const DevPeriodParams &pp, double inventory, int *err) {
+  if (inventory < pp.min_inventory || inventory > pp.max_inventory) *err = LSMC_ERR_ARGUMENT;
+  const double *xi = a.ratchet_inventory + pp.rbegin, *mn = a.ratchet_min + pp.rbegin, *mx = a.ratchet_max + pp.rbegin;
+  switch (pp.kind) {
+    case LSMC_CONSTRAINT_CONSTANT:
+      return {mn[0], mx[0]};
+    case LSMC_CONSTRAINT_PIECEWISE_LINEAR:
+      return {spline_dev(xi, mn, pp.rcount, inventory), spline_dev(xi, mx, pp.rcount, inventory)};
+    case LSMC_CONSTRAINT_STEP: {
+      if (inventory < xi[0] || inventory > xi[pp.rcount - 1]) *err = LSMC_ERR_ARGUMENT;
+      int idx = max(0, min(left_segment_dev(xi, pp.rcount, inventory), pp.rcount - 1));
+      return {mn[idx], mx[idx]};
+    }
+    default:
+      return {horner_dev(a.poly_min + pp.poly_begin, pp.rcount, inventory), horner_dev(a.poly_max + pp.poly_begin, pp.rcount, inventory)};
+  }
+}
+
+// StorageHelper.CalculateBangBangDecisionSet (SH.cs:109-204)
+__device__ __forceinline__ int decision_set_dev(DevRange r, double inventory, double loss, double next_min, double next_max, double tol,
+                                                int extra, double *out, int *err) {
+  const double base = inventory - loss;
+  double withdraw, inject;
+  const double lowest = r.lo + base;
+  if (lowest > next_max) {
+    if (!(lowest - next_max < tol)) *err = LSMC_ERR_ARGUMENT;
+    withdraw = next_max - base;
+  } else {
+    withdraw = lowest > next_min ? r.lo : next_min - base;
+  }
+  const double highest = r.hi + base;
+  if (highest < next_min) {
+    if (!(next_min - highest < tol)) *err = LSMC_ERR_ARGUMENT;
+    inject = next_min - base;
+  } else {
+    inject = highest < next_max ? r.hi : next_max - base;
+  }
+  int n = 0;
+  out[n++] = withdraw;
+  if (withdraw >= 0.0 || inject <= 0.0) {
+    const double step = (inject - withdraw) / (extra + 1);
+    for (int i = 0; i < extra; ++i) out[n++] = (i + 1) * step + withdraw;
+  } else {
+    const double step_w = (0 - withdraw) / (extra + 1);
+    for (int i = 0; i < extra; ++i) out[n++] = (i + 1) * step_w + withdraw;
+    out[n++] = 0.0;
+    const double step_i = (inject - 0) / (extra + 1);
+    for (int i = 0; i < extra; ++i) out[n++] = (i + 1) * step_i + 0;
+  }
+  out[n++] = inject;
+  return n;
+}
+
+// StorageHelper.BisectInventorySpace (SH.cs:280-314)
+__device__ __forceinline__ void bisect_dev(const double *grid, int n, double inventory, double tol, int *lower, int *upper, int *err) {
+  if (n == 1 && fabs(inventory - grid[0]) <= tol) {
+    *lower = *upper = 0;
+    return;
+  }
+  int left = 0, right = n - 1;
+  const int top = right;
+  while (right > left) {
+    const int mid = (left + right) / 2;
+    const double gm = grid[mid];
+    if (fabs(inventory - gm) <= tol) {
+      *lower = *upper = mid;
+      return;
+    }
+    if (gm > inventory) {
+      right = mid;
+      continue;
+    }
+    const double g1 = grid[mid + 1];
+    if (inventory <= g1) {
+      *lower = mid;
+      *upper = mid + 1;
+      return;
+    }
+    if (fabs(inventory - g1) <= tol) {
+      *lower = *upper = mid + 1;
+      return;
+    }
+    if (mid + 1 == top) break;
+    left = mid;
+  }
+  *err = LSMC_ERR_ARGUMENT;
+  *lower = *upper = (inventory < grid[0]) ? 0 : n - 1;  // keep running on the nearest point; the flag fails the run
+}
+
+template <int KP>
+__global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int K = a.K, F = a.F;
+  // dynamic smem: gamma [Gmax][K] | grid_next [Gmax] | rinv [K*K] dd | powers | warp staging
+  double *s_gamma = reinterpret_cast<double *>(smem_raw);
+  double *s_grid = s_gamma + (size_t)a.Gmax * K;
+  dd *s_rinv = reinterpret_cast<dd *>(s_grid + a.Gmax);
+  double *s_stage = reinterpret_cast<double *>(s_rinv + K * K);  // [kWarps][sums_width]
+  int32_t *s_pw = reinterpret_cast<int32_t *>(s_stage + kWarps * a.sums_width);
+  __shared__ DevPeriodParams s_pp;
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
+
+  const int64_t num_tiles = (a.N + kThreads - 1) / kThreads;
+  bool first_tile = true;
+  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, first_tile = false) {
+    const int64_t n = tile * kThreads + threadIdx.x;
+    const bool valid = n < a.N;
+    const int64_t nc = valid ? n : a.N - 1;
+    double inventory = a.start_inventory;
+    double pv_total = 0.0;
+    int err = 0;
+
+    for (int p = 0; p < a.P; ++p) {
+      __syncthreads();  // previous period's shared tables are no longer in use
+      if (threadIdx.x == 0) s_pp = a.periods[p];
+      __syncthreads();
+      const DevPeriodParams pp = s_pp;
+      const int Gn = pp.grid_next_count;
+      for (int i = threadIdx.x; i < Gn * K; i += blockDim.x) s_gamma[i] = a.gamma[(size_t)p * a.Gmax * K + i];
+      for (int i = threadIdx.x; i < Gn; i += blockDim.x) s_grid[i] = a.grids[(size_t)(p + 1) * a.Gmax + i];
+      if (!pp.mean_mode)
+        for (int i = threadIdx.x; i < K * K; i += blockDim.x)
+          s_rinv[i] = dd{a.rinv[((size_t)p * K * K + i) * 2], a.rinv[((size_t)p * K * K + i) * 2 + 1]};
+      __syncthreads();
+
+      BasisSpec b;
+      b.mean_mode = pp.mean_mode;
+      b.rinv = nullptr;
+      double price = pp.forward_price;
+      if (!pp.mean_mode) {
+        b.spot = a.spot + (size_t)pp.sim_row * a.sim_pitch;
+#pragma unroll
+        for (int i = 0; i < LSMC_MAX_FACTORS; ++i) b.factors[i] = (i < F) ? a.factors[i] + (size_t)pp.sim_row * a.sim_pitch : nullptr;
+        price = b.spot[nc];
+      }
+      double q[KP];
+      eval_q<KP>(b, s_pw, s_rinv, K, F, nc, valid, q);
+
+      // LSV.cs:445-508 for this path
+      DevRange range = storage_range_dev(a, pp, inventory, &err);
+      const double loss = pp.loss * inventory;
+      double decisions[LSMC_MAX_DECISIONS];
+      const int D = decision_set_dev(range, inventory, loss, pp.next_space_lo, pp.next_space_hi, a.tolerance, a.extra_decisions,
+                                     decisions, &err);
+      const double inv_cost_npv = (inventory * pp.inv_cost) * pp.inv_cost_df;
+      double best = 0.0, best_consumed = 0.0, best_immediate = 0.0, best_volume = 0.0;
+      int best_d = 0;
+      for (int d = 0; d < D; ++d) {
+        const double volume = decisions[d];
+        const double after = inventory + volume - loss;
+        const double consumed = (volume > 0.0 ? pp.cons_inj : pp.cons_wd) * fabs(volume);
+        const double inject_withdraw_npv = (-volume * price) * pp.settle_df;
+        const double consumed_npv = (-consumed * price) * pp.settle_df;
+        const double cost_npv = volume > 0.0 ? (pp.inj_cost * volume) * pp.inj_df : (pp.wd_cost * fabs(-volume)) * pp.wd_df;
+        const double immediate = ((inject_withdraw_npv - cost_npv) + consumed_npv) - inv_cost_npv;  // LSV.cs:473
+        int lo, hi;
+        bisect_dev(s_grid, Gn, after, a.tolerance, &lo, &hi, &err);
+        const double *gl = s_gamma + (size_t)lo * K;
+        double c_lo = q[0] * gl[0];
+#pragma unroll
+        for (int k = 1; k < KP; ++k)
+          if (k < K) c_lo = __fma_rn(q[k], gl[k], c_lo);
+        double cont = c_lo;
+        if (hi != lo) {  // InterpolateContinuationValue (LSV.cs:807-826)
+          const double *gu = s_gamma + (size_t)hi * K;
+          double c_hi = q[0] * gu[0];
+#pragma unroll
+          for (int k = 1; k < KP; ++k)
+            if (k < K) c_hi = __fma_rn(q[k], gu[k], c_hi);
+          const double lower_inv = s_grid[lo], upper_inv = s_grid[hi];
+          const double lower_w = (upper_inv - after) / (upper_inv - lower_inv);
+          const double upper_w = 1.0 - lower_w;
+          cont = c_lo * lower_w + c_hi * upper_w;
+        }
+        const double total = immediate + cont;
+        if (d == 0 || total > best) {
+          best = total;
+          best_d = d;
+          best_consumed = consumed;
+          best_immediate = immediate;
+          best_volume = volume;
+        }
+      }
+      const double next_inventory = inventory + best_volume - loss;  // LSV.cs:485
+
+      if (valid) {
+        const size_t off = (size_t)p * a.N + n;
+        if (a.p_inventory) a.p_inventory[off] = inventory;
+        if (a.p_volume) a.p_volume[off] = best_volume;
+        if (a.p_consumed) a.p_consumed[off] = best_consumed;
+        if (a.p_loss) a.p_loss[off] = loss;
+        if (a.p_net_volume) a.p_net_volume[off] = -best_volume - best_consumed;
+        if (a.p_pv) a.p_pv[off] = best_immediate;
+        if (a.p_decision) a.p_decision[off] = (double)best_d;
+      }
+
+      // per-period sums (LSV.cs:490-507, 510): fixed-order reduction over the CTA
+      double sums[8];
+      sums[0] = valid ? -(best_volume + best_consumed) * price : 0.0;
+      sums[1] = valid ? best_volume : 0.0;
+      sums[2] = valid ? best_consumed : 0.0;
+      sums[3] = valid ? loss : 0.0;
+      sums[4] = valid ? best_immediate : 0.0;
+      sums[5] = valid ? inventory : 0.0;
+      sums[6] = 0.0;
+      sums[7] = 0.0;
+      int kidx;
+      double total = warp_reduce8(sums, lane, kidx);
+      if ((lane & 3) == 0) s_stage[warp * a.sums_width + kidx] = total;
+      for (int half = 0; half < KP; half += 8) {
+        double part[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) part[k] = (half + k < KP) ? q[(half + k < KP) ? half + k : 0] : 0.0;
+        total = warp_reduce8(part, lane, kidx);
+        if ((lane & 3) == 0 && half + kidx < K) s_stage[warp * a.sums_width + kForwardSums + half + kidx] = total;
+      }
+      __syncthreads();
+      if (threadIdx.x < a.sums_width) {
+        double t = s_stage[threadIdx.x];
+        for (int w = 1; w < kWarps; ++w) t += s_stage[w * a.sums_width + threadIdx.x];
+        double *dst = a.step_sums + ((size_t)p * gridDim.x + blockIdx.x) * a.sums_width + threadIdx.x;
+        *dst = first_tile ? t : *dst + t;
+      }
+      if (valid) pv_total += best_immediate;
+      inventory = next_inventory;
+    }
+    if (valid) {
+      a.pv_by_sim[n] = pv_total;
+      a.final_inventory[n] = inventory;
+      if (a.p_inventory) a.p_inventory[(size_t)a.P * a.N + n] = inventory;
+    }
+    if (err) atomicExch(a.error_flag, err);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Deterministic sums
+// ------------------------------------------------------------------------------------------------------------------
+// out[block] = sum over this block's slice of (x[i] - shift)^power, power in {1,2}
+__global__ void __launch_bounds__(256) sum_kernel(const double *__restrict__ x, int64_t n, double shift, int power, double *out) {
+  __shared__ double s_w[8];
+  const int64_t per_block = (n + gridDim.x - 1) / gridDim.x;
+  const int64_t begin = (int64_t)blockIdx.x * per_block, end = min(begin + per_block, n);
+  double acc = 0.0;
+  for (int64_t i = begin + threadIdx.x; i < end; i += blockDim.x) {
+    double d = x[i] - shift;
+    acc += (power == 2) ? d * d : d;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(kFullMask, acc, off);
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += s_w[w];
+    out[blockIdx.x] = t;
+  }
+}
+
+__global__ void combine_ranks_kernel(const double *__restrict__ all, int world, int count, int K, int mean_mode, double total_paths,
+                                     double *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  double t = 0.0;
+  for (int r = 0; r < world; ++r) t += all[(size_t)r * count + i];
+  if (mean_mode) t = (i % K == 0) ? t / total_paths : 0.0;
+  out[i] = t;
+}
+
+// out[p][j] = sum over CTAs of step_sums[p][cta][j], in CTA order
+__global__ void reduce_step_sums_kernel(const double *__restrict__ in, int num_ctas, int width, double *out) {
+  const int p = blockIdx.x;
+  for (int j = threadIdx.x; j < width; j += blockDim.x) {
+    double t = 0.0;
+    for (int c = 0; c < num_ctas; ++c) t += in[((size_t)p * num_ctas + c) * width + j];
+    out[(size_t)p * width + j] = t;
+  }
+}
+
+template <int KP>
+void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
+  switch (which) {
+    case 0:
+      gram_kernel<KP><<<grid, block, 0, stream>>>(*static_cast<const GramArgs *>(args));
+      break;
+    case 1:
+      cholesky_kernel<KP><<<grid, block, 0, stream>>>(*static_cast<const CholeskyArgs *>(args));
+      break;
+    case 2:
+      if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      backward_step_kernel<KP><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
+      break;
+    case 3:
+      if (smem > 48 * 1024) cudaFuncSetAttribute(forward_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      forward_kernel<KP><<<grid, block, smem, stream>>>(*static_cast<const ForwardArgs *>(args));
+      break;
+  }
+}
+
+void dispatch(int KP, int which, const void *args, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
+  switch (KP) {
+    case 1: launch_for_k<1>(which, args, grid, block, smem, stream); break;
+    case 2: launch_for_k<2>(which, args, grid, block, smem, stream); break;
+    case 3: launch_for_k<3>(which, args, grid, block, smem, stream); break;
+    case 4: launch_for_k<4>(which, args, grid, block, smem, stream); break;
+    case 5: launch_for_k<5>(which, args, grid, block, smem, stream); break;
+    case 6: launch_for_k<6>(which, args, grid, block, smem, stream); break;
+    case 7: launch_for_k<7>(which, args, grid, block, smem, stream); break;
+    case 8: launch_for_k<8>(which, args, grid, block, smem, stream); break;
+    case 12: launch_for_k<12>(which, args, grid, block, smem, stream); break;
+    default: launch_for_k<16>(which, args, grid, block, smem, stream); break;
+  }
+}
+
+}  // namespace
+
+int padded_basis(int K) { return K <= 8 ? K : (K <= 12 ? 12 : 16); }
+
+size_t backward_smem_bytes(int KP, int D, int K, int F, int acc_k) {
+  auto up = [](size_t b) { return (b + 15) & ~size_t(15); };
+  return up(sizeof(DevDecision) * kMaxGridTile * D) + up(sizeof(double) * kMaxGridTile * D * KP) + up(sizeof(double) * kMaxGridTile) +
+         up(sizeof(int32_t) * kMaxGridTile) + 2 * up(sizeof(dd) * K * K) + up(sizeof(int32_t) * K * (1 + F)) +
+         up(sizeof(double) * kWarps * kMaxGridTile * acc_k);
+}
+
+size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width) {
+  return sizeof(double) * ((size_t)Gmax * K + Gmax) + sizeof(dd) * K * K + sizeof(double) * kWarps * sums_width +
+         sizeof(int32_t) * K * (1 + F) + 16;
+}
+
+void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream) {
+  dispatch(padded_basis(a.K), 0, &a, dim3(num_chunks, num_slots), dim3(kThreads), 0, stream);
+}
+void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream) {
+  dispatch(padded_basis(a.K), 1, &a, dim3(num_slots), dim3(64), 0, stream);
+}
+void launch_backward_step(const BackwardStepArgs &a, int num_chunks, cudaStream_t stream) {
+  const int KP = padded_basis(a.K);
+  const int gtiles = (a.G + kMaxGridTile - 1) / kMaxGridTile;
+  dispatch(KP, 2, &a, dim3(gtiles, num_chunks), dim3(kThreads), backward_smem_bytes(KP, a.D, a.K, a.F, a.acc_k), stream);
+}
+void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream) {
+  const int threads = 256 / a.acc_k * a.acc_k;
+  reduce_partials_kernel<<<a.G, threads, 0, stream>>>(a);
+}
+void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream) {
+  dispatch(padded_basis(a.K), 3, &a, dim3(num_ctas), dim3(kThreads), forward_smem_bytes(a.K, a.F, a.Gmax, a.sums_width), stream);
+}
+void launch_combine_ranks(const double *all, int world, int count, int K, int mean_mode, double total_paths, double *out,
+                          cudaStream_t stream) {
+  combine_ranks_kernel<<<(count + 127) / 128, 128, 0, stream>>>(all, world, count, K, mean_mode, total_paths, out);
+}
+void launch_reduce_step_sums(const double *in, int P, int num_ctas, int width, double *out, cudaStream_t stream) {
+  reduce_step_sums_kernel<<<P, 32, 0, stream>>>(in, num_ctas, width, out);
+}
+void launch_sum(const double *x, int64_t n, double shift, int power, double *out, int blocks, cudaStream_t stream) {
+  sum_kernel<<<blocks, 256, 0, stream>>>(x, n, shift, power, out);
+}
+
+}  // namespace lsmc

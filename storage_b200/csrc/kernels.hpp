@@ -1,0 +1,53 @@
+// kernels.hpp — launch interface between lsmc_api.cu (host orchestration) and kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+#include "device_types.hpp"
+
+namespace lsmc {
+
+struct GramArgs {
+  int64_t N;
+  int64_t chunk_paths;     // paths per CTA
+  int K, F;
+  const BasisSpec *specs;  // [num_slots] device array: one per regression period
+  const int32_t *powers;   // [K][1+F]
+  double *partials;        // [num_slots][num_chunks][KP*(KP+1)/2][2]
+};
+
+struct CholeskyArgs {
+  int K;
+  int num_ranks, num_slots, num_chunks;
+  const double *partials;  // [num_ranks][num_slots][num_chunks][NP][2], summed in (rank, chunk) order
+  double *rinv;            // [num_slots][K*K*2]
+  int32_t *error_flag;
+};
+
+struct ReduceArgs {
+  const double *partials;  // [num_chunks][G][acc_k]
+  int num_chunks, G, K, acc_k;
+  int mean_mode;
+  int64_t total_paths;
+  double *out;             // [G][K]
+};
+
+int padded_basis(int K);
+inline int acc_width(int K) { return padded_basis(K) <= 8 ? 8 : 16; }
+size_t backward_smem_bytes(int KP, int D, int K, int F, int acc_k);
+size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width);
+
+void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream);
+void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream);
+void launch_backward_step(const BackwardStepArgs &a, int num_chunks, cudaStream_t stream);
+void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);
+void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream);
+// out[i] = sum over ranks r of all[r][i] (rank order); mean_mode: component 0 of every K-vector divided by total_paths, rest 0
+void launch_combine_ranks(const double *all, int world, int count, int K, int mean_mode, double total_paths, double *out,
+                          cudaStream_t stream);
+void launch_reduce_step_sums(const double *in, int P, int num_ctas, int width, double *out, cudaStream_t stream);
+void launch_sum(const double *x, int64_t n, double shift, int power, double *out, int blocks, cudaStream_t stream);
+
+}  // namespace lsmc

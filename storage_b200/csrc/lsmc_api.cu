@@ -1,0 +1,1001 @@
+// lsmc_api.cu — the C ABI of include/lsmc_b200.h: handle life cycle, host orchestration of the backward induction
+// and forward simulation on one B200, result marshalling.  No CPU fallback: every compute entry point fails with
+// LSMC_ERR_CUDA when there is no usable device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "comm.hpp"
+#include "device_types.hpp"
+#include "host_model.hpp"
+#include "kernels.hpp"
+#include "simulate.hpp"
+
+using namespace lsmc;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct CudaFailure : std::runtime_error {
+  explicit CudaFailure(const std::string &m) : std::runtime_error(m) {}
+};
+
+#define CUDA_OK(expr)                                                                                          \
+  do {                                                                                                         \
+    cudaError_t err__ = (expr);                                                                                \
+    if (err__ != cudaSuccess)                                                                                  \
+      throw CudaFailure(std::string(#expr) + " failed: " + cudaGetErrorString(err__) + " (" __FILE__ ":" +     \
+                        std::to_string(__LINE__) + ")");                                                       \
+  } while (0)
+
+template <class T>
+struct DeviceBuffer {
+  T *ptr = nullptr;
+  size_t count = 0;
+  DeviceBuffer() = default;
+  DeviceBuffer(const DeviceBuffer &) = delete;
+  DeviceBuffer &operator=(const DeviceBuffer &) = delete;
+  ~DeviceBuffer() { release(); }
+  void release() {
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    count = 0;
+  }
+  void allocate(size_t n) {
+    release();
+    if (n == 0) n = 1;
+    CUDA_OK(cudaMalloc(&ptr, n * sizeof(T)));
+    count = n;
+  }
+  void upload(const std::vector<T> &host) {
+    allocate(host.size());
+    if (!host.empty()) CUDA_OK(cudaMemcpy(ptr, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
+  }
+};
+
+struct SimSet {
+  bool ready = false;
+  const double *spot = nullptr;  // [rows][N] device
+  const double *factors[LSMC_MAX_FACTORS] = {};
+  DeviceBuffer<double> owned_spot;
+  DeviceBuffer<double> owned_factors[LSMC_MAX_FACTORS];
+  double ms_simulation = 0.0;
+};
+
+}  // namespace
+
+struct lsmc_handle {
+  std::string error;
+  int device = 0;
+  // problem
+  int64_t N = 0;
+  int P = 0, K = 0, F = 0, KP = 0;
+  bool current_active = false, discount_deltas = false, compat_terminal = true;
+  uint32_t flags = 0;
+  bool want_decisions = true;
+  double inventory = 0, tolerance = 1e-10, grid_spacing = 0;
+  int extra = 0;
+  std::vector<double> forward_price, settle_df;
+  std::vector<int32_t> powers;
+  std::unique_ptr<StorageModel> model;
+  ValuationTables tables;
+  int first_sim = 0, sim_rows = 0;
+  int64_t pitch = 0;
+  int Gmax = 0, D = 0, acc_k = 8;
+
+  cudaStream_t stream = nullptr;
+  SimSet sims[2];
+  DeviceBuffer<double> v_a, v_b, grids, gamma, rinv, partials, gram_partials, inv_cost, pv, final_inv, step_sums, step_totals,
+      block_sums, gather_buf, ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
+  DeviceBuffer<DevDecision> decisions;
+  DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
+  DeviceBuffer<DevPeriodParams> period_params;
+  DeviceBuffer<BasisSpec> gram_specs;
+  DeviceBuffer<double> panels[7];  // inventory, volume, consumed, loss, net volume, pv, decision index
+  std::vector<size_t> table_offset;  // per period: first grid point in the concatenated tables
+
+  Comm comm;  // single rank unless lsmc_comm_init was called
+
+  // results of the last run
+  bool has_results = false;
+  lsmc_results scalars{};
+  std::vector<double> deltas, profile, pv_by_sim;
+  std::vector<lsmc_trigger_prices> trigger;
+  std::vector<double> h_gamma, h_rinv;
+};
+
+namespace {
+
+int status_of(lsmc_handle *h, const std::exception &e) {
+  if (auto *le = dynamic_cast<const Error *>(&e)) {
+    if (h) h->error = le->what();
+    else g_create_error = le->what();
+    return le->status;
+  }
+  if (h) h->error = e.what();
+  else g_create_error = e.what();
+  return dynamic_cast<const CudaFailure *>(&e) ? LSMC_ERR_CUDA : LSMC_ERR_ARGUMENT;
+}
+
+void require_device(int device) {
+  int count = 0;
+  cudaError_t err = cudaGetDeviceCount(&count);
+  if (err != cudaSuccess || count == 0)
+    throw CudaFailure(std::string("no CUDA device available (") + cudaGetErrorString(err) +
+                      "); liblsmc_b200 has no CPU fallback");
+  if (device < 0 || device >= count) throw CudaFailure("CUDA device index out of range");
+  CUDA_OK(cudaSetDevice(device));
+}
+
+BasisSpec basis_spec(const lsmc_handle &h, int which, int period) {
+  BasisSpec b{};
+  if (period == 0 && h.current_active) {
+    b.mean_mode = 1;
+    return b;
+  }
+  const SimSet &s = h.sims[which];
+  const size_t row = (size_t)(period - h.first_sim) * h.N;
+  b.spot = s.spot + row;
+  for (int i = 0; i < h.F; ++i) b.factors[i] = s.factors[i] + row;
+  b.rinv = h.rinv.ptr + (size_t)period * h.K * h.K * 2;
+  b.mean_mode = 0;
+  return b;
+}
+
+struct Timer {
+  cudaEvent_t a, b;
+  cudaStream_t s;
+  explicit Timer(cudaStream_t stream) : s(stream) {
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+  }
+  ~Timer() {
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+  }
+  void start() { cudaEventRecord(a, s); }
+  void stop() { cudaEventRecord(b, s); }
+  double ms() {
+    cudaEventSynchronize(b);
+    float m = 0;
+    cudaEventElapsedTime(&m, a, b);
+    return m;
+  }
+};
+
+double device_sum(lsmc_handle *h, const double *x, int64_t n, double shift, int power) {
+  const int blocks = (int)std::min<int64_t>(512, std::max<int64_t>(1, (n + 4095) / 4096));
+  if (h->block_sums.count < 512) h->block_sums.allocate(512);
+  launch_sum(x, n, shift, power, h->block_sums.ptr, blocks, h->stream);
+  h->scalars.kernel_launches++;
+  std::vector<double> host(blocks);
+  CUDA_OK(cudaMemcpyAsync(host.data(), h->block_sums.ptr, blocks * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CUDA_OK(cudaStreamSynchronize(h->stream));
+  double t = 0.0;
+  for (double v : host) t += v;
+  return t;
+}
+
+// AverageContinuationValue (LSV.cs:785-805) from the per-period basis column means: mean_n(q_n . gamma) = qbar . gamma
+double average_continuation(const lsmc_handle &h, int p, const double *qbar, double after) {
+  const std::vector<double> &grid = h.tables.periods[p + 1].grid;
+  int lo, hi;
+  bisect_inventory_space(grid.data(), (int)grid.size(), after, h.tolerance, &lo, &hi);
+  auto dot = [&](int g) {
+    const double *gm = &h.h_gamma[((size_t)p * h.Gmax + g) * h.K];
+    double s = 0.0;
+    for (int k = 0; k < h.K; ++k) s += qbar[k] * gm[k];
+    return s;
+  };
+  if (lo == hi) return dot(lo);
+  const double lower_w = (grid[hi] - after) / (grid[hi] - grid[lo]);
+  const double upper_w = 1.0 - lower_w;
+  return dot(lo) * lower_w + dot(hi) * upper_w;
+}
+
+// Trigger prices of period p at the expected inventory (LSV.cs:523-592, 704-755)
+void trigger_prices_for_period(const lsmc_handle &h, int p, double expected_inventory, const double *qbar, lsmc_trigger_prices &tp) {
+  const StorageModel &st = *h.model;
+  std::memset(&tp, 0, sizeof(tp));
+  const double loss = st.loss_fraction(p) * expected_inventory;
+  RateRange range = st.inject_withdraw_range(p, expected_inventory);
+  double dset[LSMC_MAX_DECISIONS];
+  const int D = bang_bang_decision_set(range, expected_inventory, loss, h.tables.space_lo[p + 1], h.tables.space_hi[p + 1], h.tolerance,
+                                       h.extra, dset);
+  const double df = h.settle_df[p];
+  auto price_for = [&](double volume, double alt_cont, double alt_volume, double alt_cost, double alt_consumed) {
+    const double cont = average_continuation(h, p, qbar, expected_inventory + volume - loss);
+    const double cont_change = cont - alt_cont;
+    const double excess = volume - alt_volume;
+    const double cost_change = st.decision_cost_npv(p, volume) - alt_cost;
+    const double consumed_change = st.decision_consumed(p, volume) - alt_consumed;
+    return (cont_change - cost_change) / (df * (excess + consumed_change));
+  };
+  constexpr int NV = LSMC_NUM_TRIGGER_VOLUMES;
+  const double max_inject = *std::max_element(dset, dset + D);
+  if (max_inject > 0) {
+    double alt = 0.0;
+    bool have = false;
+    for (int i = 0; i < D; ++i)
+      if (dset[i] >= 0 && (!have || dset[i] < alt)) alt = dset[i], have = true;
+    if (max_inject > alt) {
+      const double alt_cont = average_continuation(h, p, qbar, expected_inventory + alt - loss);
+      const double alt_cost = st.decision_cost_npv(p, alt), alt_cons = st.decision_consumed(p, alt);
+      const double inc = (max_inject - alt) / NV;
+      for (int i = 1; i < NV; ++i) tp.inject_volume[i - 1] = alt + i * inc;
+      tp.inject_volume[NV - 1] = max_inject;
+      for (int i = 0; i < NV; ++i) tp.inject_price[i] = price_for(tp.inject_volume[i], alt_cont, alt, alt_cost, alt_cons);
+      tp.num_inject = NV;
+      tp.has_inject_price = 1;
+      tp.max_inject_trigger_price = tp.inject_price[NV - 1];
+      tp.max_inject_volume = max_inject;
+    }
+  }
+  const double max_withdraw = *std::min_element(dset, dset + D);
+  if (max_withdraw < 0) {
+    double alt = 0.0;
+    bool have = false;
+    for (int i = 0; i < D; ++i)
+      if (dset[i] <= 0 && (!have || dset[i] > alt)) alt = dset[i], have = true;
+    if (max_withdraw < alt) {
+      const double alt_cont = average_continuation(h, p, qbar, expected_inventory + alt - loss);
+      const double alt_cost = st.decision_cost_npv(p, alt), alt_cons = st.decision_consumed(p, alt);
+      const double inc = (alt - max_withdraw) / NV;
+      for (int i = 0; i < NV; ++i) {  // volumes ascend from the max withdrawal; the reference lists them reversed
+        const double v = max_withdraw + (NV - 1 - i) * inc;
+        tp.withdraw_volume[i] = v;
+        tp.withdraw_price[i] = price_for(v, alt_cont, alt, alt_cost, alt_cons);
+      }
+      tp.num_withdraw = NV;
+      tp.has_withdraw_price = 1;
+      tp.max_withdraw_trigger_price = tp.withdraw_price[0];
+      tp.max_withdraw_volume = max_withdraw;
+    }
+  }
+}
+
+void build_device_tables(lsmc_handle *h) {
+  const int P = h->P, D = h->D, Gmax = h->Gmax;
+  std::vector<DevDecision> dec;
+  std::vector<int32_t> nd;
+  std::vector<double> invc;
+  h->table_offset.assign(P + 1, 0);
+  size_t total = 0;
+  for (int p = 0; p < P; ++p) {
+    h->table_offset[p] = total;
+    total += h->tables.periods[p].grid.size();
+  }
+  h->table_offset[P] = total;
+  dec.resize(total * D);
+  nd.resize(total);
+  invc.resize(total);
+  for (int p = 0; p < P; ++p) {
+    const PeriodTables &pt = h->tables.periods[p];
+    const size_t off = h->table_offset[p];
+    for (size_t g = 0; g < pt.grid.size(); ++g) {
+      nd[off + g] = pt.num_decisions[g];
+      invc[off + g] = pt.inventory_cost[g];
+      for (int d = 0; d < D; ++d) {
+        const DecisionEntry &e = pt.decisions[g * D + d];
+        dec[(off + g) * D + d] = DevDecision{e.volume, e.cost_npv, e.consumed, e.lower_w, e.upper_w, e.lower, e.upper};
+      }
+    }
+  }
+  h->decisions.upload(dec);
+  h->num_decisions.upload(nd);
+  h->inv_cost.upload(invc);
+
+  std::vector<double> grids((size_t)(P + 1) * Gmax, 0.0);
+  for (int p = 0; p <= P; ++p) std::copy(h->tables.periods[p].grid.begin(), h->tables.periods[p].grid.end(), grids.begin() + (size_t)p * Gmax);
+  h->grids.upload(grids);
+
+  const StorageModel &st = *h->model;
+  std::vector<DevPeriodParams> pp(P);
+  for (int p = 0; p < P; ++p) {
+    DevPeriodParams &d = pp[p];
+    d.min_inventory = st.min_inventory(p);
+    d.max_inventory = st.max_inventory(p);
+    d.inj_cost = st.inj_cost_[p];
+    d.inj_df = st.inj_df_[p];
+    d.wd_cost = st.wd_cost_[p];
+    d.wd_df = st.wd_df_[p];
+    d.cons_inj = st.cons_inj_[p];
+    d.cons_wd = st.cons_wd_[p];
+    d.loss = st.loss_[p];
+    d.inv_cost = st.inv_cost_[p];
+    d.inv_cost_df = st.inv_cost_df_[p];
+    d.next_space_lo = h->tables.space_lo[p + 1];
+    d.next_space_hi = h->tables.space_hi[p + 1];
+    d.settle_df = h->settle_df[p];
+    d.forward_price = h->forward_price[p];
+    d.delta_df = h->discount_deltas ? h->settle_df[p] : 1.0;
+    d.kind = st.kind_[p];
+    d.rbegin = st.rbegin_[p];
+    d.rcount = st.rcount_[p];
+    d.poly_begin = st.poly_begin_[p] < 0 ? 0 : st.poly_begin_[p];
+    d.grid_next_count = (int32_t)h->tables.periods[p + 1].grid.size();
+    d.mean_mode = (p == 0 && h->current_active) ? 1 : 0;
+    d.sim_row = d.mean_mode ? -1 : p - h->first_sim;
+    d.pad = 0;
+  }
+  h->period_params.upload(pp);
+  h->ratchet_inv.upload(st.r_inv_);
+  h->ratchet_min.upload(st.r_min_);
+  h->ratchet_max.upload(st.r_max_);
+  h->poly_min.upload(st.poly_min_);
+  h->poly_max.upload(st.poly_max_);
+  h->d_powers.upload(h->powers);
+}
+
+void validate_problem(const lsmc_problem *pb) {
+  if (!pb) throw Error(LSMC_ERR_ARGUMENT, "problem is null");
+  if (pb->inventory < 0) throw Error(LSMC_ERR_ARGUMENT, "Inventory cannot be negative.");  // LSV.cs:64-65
+  if (pb->storage.num_periods < 1) throw Error(LSMC_ERR_ARGUMENT, "Storage has expired");
+  if (pb->num_sims <= 0) throw Error(LSMC_ERR_ARGUMENT, "Number of simulations must be positive.");
+  if (pb->num_basis < 1 || pb->num_basis > LSMC_MAX_BASIS) throw Error(LSMC_ERR_ARGUMENT, "Number of basis functions must be in [1, LSMC_MAX_BASIS].");
+  if (pb->num_factors < 0 || pb->num_factors > LSMC_MAX_FACTORS) throw Error(LSMC_ERR_ARGUMENT, "Number of factors must be in [0, LSMC_MAX_FACTORS].");
+  if (pb->extra_decisions < 0) throw Error(LSMC_ERR_INVALID_OPERATION, "ExtraDecisions must be non-negative.");  // LVP.cs:137-138
+  if (2 * pb->extra_decisions + 3 > LSMC_MAX_DECISIONS) throw Error(LSMC_ERR_ARGUMENT, "ExtraDecisions too large for LSMC_MAX_DECISIONS.");
+  if (!(pb->grid_spacing > 0.0)) throw Error(LSMC_ERR_ARGUMENT, "Grid spacing must be positive.");
+  if (!pb->forward_price || !pb->settle_df || !pb->basis_powers) throw Error(LSMC_ERR_INVALID_OPERATION, "ForwardCurve, SettleDateRule and BasisFunctions must be set.");
+  for (int i = 0; i < pb->num_basis * (1 + pb->num_factors); ++i)
+    if (pb->basis_powers[i] < 0 || pb->basis_powers[i] > 64) throw Error(LSMC_ERR_ARGUMENT, "Spot power and Markov factor powers must be non-negative.");
+}
+
+void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const volatile int *cancel) {
+  CUDA_OK(cudaSetDevice(h->device));
+  if (!h->sims[0].ready) throw Error(LSMC_ERR_INVALID_OPERATION, "RegressionSpotSimsGenerator has not been set.");
+  if (!h->sims[1].ready) throw Error(LSMC_ERR_INVALID_OPERATION, "ValuationSpotSimsGenerator has not been set.");
+  const int P = h->P, K = h->K, F = h->F, D = h->D, Gmax = h->Gmax;
+  const int64_t N = h->N;
+  cudaStream_t st = h->stream;
+  h->has_results = false;
+  h->scalars = lsmc_results{};
+  h->scalars.ms_regression_sim = h->sims[0].ms_simulation;
+  h->scalars.ms_valuation_sim = h->sims[1].ms_simulation;
+  int64_t &launches = h->scalars.kernel_launches;
+  auto wall0 = std::chrono::steady_clock::now();
+  int32_t zero = 0;
+  CUDA_OK(cudaMemcpyAsync(h->error_flag.ptr, &zero, sizeof(zero), cudaMemcpyHostToDevice, st));
+  auto cancelled = [&] { return cancel && *cancel != 0; };
+  auto check_cancel = [&] {
+    if (cancelled()) {
+      cudaStreamSynchronize(st);
+      throw Error(LSMC_ERR_CANCELLED, "The operation was canceled.");
+    }
+  };
+  check_cancel();
+
+  Timer t_pinv(st), t_back(st), t_fwd(st);
+  // ---- regression pre-pass: Gram matrices, Cholesky factors and R^-1 of every regression period (LSV.cs:191-196)
+  const int first_reg = h->current_active ? 1 : 0;
+  const int num_slots = P - first_reg;
+  t_pinv.start();
+  if (num_slots > 0) {
+    const int NP = h->KP * (h->KP + 1) / 2;
+    int64_t chunk_paths = ((N + 63) / 64 + kThreads - 1) / kThreads * kThreads;
+    chunk_paths = std::max<int64_t>(chunk_paths, 4 * kThreads);
+    const int num_chunks = (int)((N + chunk_paths - 1) / chunk_paths);
+    const int world = h->comm.world();
+    std::vector<BasisSpec> specs(num_slots);
+    for (int s = 0; s < num_slots; ++s) specs[s] = basis_spec(*h, 0, first_reg + s);
+    h->gram_specs.upload(specs);
+    // every rank's partial Gram matrices, gathered as [rank][slot][chunk][NP][2]; the Cholesky kernel sums them in
+    // (rank, chunk) order so all ranks obtain bit-identical factors
+    const size_t local_count = (size_t)num_slots * num_chunks * NP * 2;
+    h->gram_partials.allocate(local_count * world);
+    GramArgs ga{};
+    ga.N = N;
+    ga.chunk_paths = chunk_paths;
+    ga.K = K;
+    ga.F = F;
+    ga.specs = h->gram_specs.ptr;
+    ga.powers = h->d_powers.ptr;
+    ga.partials = h->gram_partials.ptr + (size_t)h->comm.rank() * local_count;
+    launch_gram(ga, num_chunks, num_slots, st);
+    launches++;
+    if (world > 1) h->comm.all_gather(ga.partials, h->gram_partials.ptr, local_count, st);
+    CholeskyArgs ca{};
+    ca.K = K;
+    ca.num_ranks = world;
+    ca.num_slots = num_slots;
+    ca.num_chunks = num_chunks;
+    ca.partials = h->gram_partials.ptr;
+    ca.rinv = h->rinv.ptr + (size_t)first_reg * K * K * 2;
+    ca.error_flag = h->error_flag.ptr;
+    launch_cholesky(ca, num_slots, st);
+    launches++;
+  }
+  t_pinv.stop();
+
+  // ---- backward induction (LSV.cs:111-131, 169-346)
+  t_back.start();
+  const int64_t num_tiles = (N + kTilePaths - 1) / kTilePaths;
+  int sm_count = 148;
+  cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device);
+  auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this) {
+    const PeriodTables &pt = h->tables.periods[p];
+    BackwardStepArgs a{};
+    a.N = N;
+    a.pitch = h->pitch;
+    a.G = (int)pt.grid.size();
+    a.Gn = terminal ? 0 : (int)h->tables.periods[p + 1].grid.size();
+    a.D = terminal ? 0 : D;
+    a.K = K;
+    a.F = F;
+    a.v_next = v_next;
+    a.v_this = v_this;
+    a.powers = h->d_powers.ptr;
+    a.acc_k = h->acc_k;
+    a.terminal_mode = terminal ? 1 : 0;
+    if (terminal) {
+      a.grid_this = h->grids.ptr + (size_t)p * Gmax;
+      a.spot = h->sims[0].spot + (size_t)(p - h->first_sim) * N;
+      std::memcpy(a.terminal, h->model->terminal_, sizeof(a.terminal));
+    } else {
+      a.gamma = h->gamma.ptr + (size_t)p * Gmax * K;
+      a.decisions = h->decisions.ptr + h->table_offset[p] * D;
+      a.num_decisions = h->num_decisions.ptr + h->table_offset[p];
+      a.inventory_cost = h->inv_cost.ptr + h->table_offset[p];
+      a.settle_df = h->settle_df[p];
+      a.basis_this = basis_spec(*h, 0, p);
+      if (a.basis_this.mean_mode) {
+        a.spot = nullptr;
+        a.const_price = h->forward_price[p];
+      } else {
+        a.spot = a.basis_this.spot;
+      }
+    }
+    a.accumulate = p > 0 ? 1 : 0;
+    if (a.accumulate) a.basis_prev = basis_spec(*h, 0, p - 1);
+    a.partials = h->partials.ptr;
+    // enough CTAs for several waves, but long enough chunks that the partial-sum traffic stays small
+    const int gtiles = (a.G + kMaxGridTile - 1) / kMaxGridTile;
+    int64_t want_chunks = std::max<int64_t>(1, (int64_t)sm_count * 24 / gtiles);
+    int tiles_per_chunk = (int)std::max<int64_t>(1, std::min<int64_t>(16, num_tiles / want_chunks));
+    const int num_chunks = (int)((num_tiles + tiles_per_chunk - 1) / tiles_per_chunk);
+    a.tiles_per_chunk = tiles_per_chunk;
+    launch_backward_step(a, num_chunks, st);
+    launches++;
+    return num_chunks;
+  };
+  auto reduce_gamma = [&](int p, int G_next, int num_chunks) {
+    // regression coefficients of V_{p+1} on period p's basis (LSV.cs:199-212) from the partial sums the kernel that
+    // produced V_{p+1} left behind
+    const bool mean_mode = (p == 0 && h->current_active);
+    ReduceArgs r{};
+    r.partials = h->partials.ptr;
+    r.num_chunks = num_chunks;
+    r.G = G_next;
+    r.K = K;
+    r.acc_k = h->acc_k;
+    r.mean_mode = mean_mode ? 1 : 0;
+    r.total_paths = h->comm.total_sims(N);
+    double *dst = h->gamma.ptr + (size_t)p * Gmax * K;
+    const int world = h->comm.world();
+    if (world == 1) {
+      r.out = dst;
+      launch_reduce_partials(r, st);
+      launches++;
+    } else {
+      // local sums -> all-gather -> sum in rank order (identical on every rank)
+      const int count = G_next * K;
+      if (h->gather_buf.count < (size_t)count * world) h->gather_buf.allocate((size_t)Gmax * K * world);
+      r.mean_mode = 0;
+      r.out = h->gather_buf.ptr + (size_t)h->comm.rank() * count;
+      launch_reduce_partials(r, st);
+      h->comm.all_gather(r.out, h->gather_buf.ptr, count, st);
+      launch_combine_ranks(h->gather_buf.ptr, world, count, K, mean_mode ? 1 : 0, (double)r.total_paths, dst, st);
+      launches += 2;
+    }
+  };
+
+  double *v_next = h->v_a.ptr, *v_this = h->v_b.ptr;
+  int chunks = launch_step(P, true, nullptr, v_next);
+  const double back_step = 0.66 / P;  // BackwardPcntTime (LSV.cs:48,164)
+  double prog = 0.0;
+  for (int p = P - 1; p >= 0; --p) {
+    check_cancel();
+    reduce_gamma(p, (int)h->tables.periods[p + 1].grid.size(), chunks);
+    chunks = launch_step(p, false, v_next, v_this);
+    std::swap(v_next, v_this);
+    prog += back_step;
+    if (progress) progress(prog, user);
+  }
+  const double *v_first = v_next;  // storage value by sim at period 0
+  t_back.stop();
+  check_cancel();
+
+  // ---- forward simulation (LSV.cs:390-521)
+  t_fwd.start();
+  const int sums_width = kForwardSums + K;
+  const int fwd_ctas = (int)std::min<int64_t>((N + kThreads - 1) / kThreads, (int64_t)sm_count * 8);
+  h->step_sums.allocate((size_t)P * fwd_ctas * sums_width);
+  h->step_totals.allocate((size_t)P * sums_width);
+  ForwardArgs fa{};
+  fa.N = N;
+  fa.P = P;
+  fa.K = K;
+  fa.F = F;
+  fa.Gmax = Gmax;
+  fa.sim_pitch = N;
+  fa.periods = h->period_params.ptr;
+  fa.ratchet_inventory = h->ratchet_inv.ptr;
+  fa.ratchet_min = h->ratchet_min.ptr;
+  fa.ratchet_max = h->ratchet_max.ptr;
+  fa.poly_min = h->poly_min.ptr;
+  fa.poly_max = h->poly_max.ptr;
+  fa.grids = h->grids.ptr;
+  fa.gamma = h->gamma.ptr;
+  fa.rinv = h->rinv.ptr;
+  fa.powers = h->d_powers.ptr;
+  fa.spot = h->sims[1].spot;
+  for (int i = 0; i < F; ++i) fa.factors[i] = h->sims[1].factors[i];
+  fa.start_inventory = h->inventory;
+  fa.tolerance = h->tolerance;
+  fa.extra_decisions = h->extra;
+  fa.pv_by_sim = h->pv.ptr;
+  fa.final_inventory = h->final_inv.ptr;
+  fa.step_sums = h->step_sums.ptr;
+  fa.sums_width = sums_width;
+  fa.p_inventory = h->panels[0].ptr;
+  fa.p_volume = h->panels[1].ptr;
+  fa.p_consumed = h->panels[2].ptr;
+  fa.p_loss = h->panels[3].ptr;
+  fa.p_net_volume = h->panels[4].ptr;
+  fa.p_pv = h->panels[5].ptr;
+  fa.p_decision = h->panels[6].ptr;
+  fa.error_flag = h->error_flag.ptr;
+  launch_forward(fa, fwd_ctas, st);
+  launches++;
+  launch_reduce_step_sums(h->step_sums.ptr, P, fwd_ctas, sums_width, h->step_totals.ptr, st);
+  launches++;
+  t_fwd.stop();
+
+  std::vector<double> sums((size_t)P * sums_width);
+  CUDA_OK(cudaMemcpyAsync(sums.data(), h->step_totals.ptr, sums.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  h->h_gamma.resize((size_t)P * Gmax * K);
+  CUDA_OK(cudaMemcpyAsync(h->h_gamma.data(), h->gamma.ptr, h->h_gamma.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  h->h_rinv.resize((size_t)P * K * K * 2);
+  CUDA_OK(cudaMemcpyAsync(h->h_rinv.data(), h->rinv.ptr, h->h_rinv.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  int32_t flag = 0;
+  CUDA_OK(cudaMemcpyAsync(&flag, h->error_flag.ptr, sizeof(flag), cudaMemcpyDeviceToHost, st));
+  CUDA_OK(cudaStreamSynchronize(st));
+  CUDA_OK(cudaGetLastError());
+  if (flag == LSMC_ERR_NUMERICAL)
+    throw Error(LSMC_ERR_NUMERICAL, "Regression design matrix is rank deficient on the simulated paths (the reference's QR would return non-finite coefficients).");
+  if (flag != 0)
+    throw Error((lsmc_status)flag, "A simulated path left the feasible inventory region during the forward simulation (inventory outside its limits or outside the inventory grid).");
+  h->comm.all_reduce_host(sums.data(), sums.size(), st);
+  const double total_n = (double)h->comm.total_sims(N);
+
+  // per-period results (LSV.cs:510-518) and trigger prices (LSV.cs:523-592)
+  h->deltas.assign(P + 1, 0.0);
+  h->profile.assign((size_t)(P + 1) * 5, 0.0);
+  h->trigger.assign(P, lsmc_trigger_prices{});
+  const double fwd_step = (1.0 - 0.66) / (P + 1);  // LSV.cs:387
+  for (int p = 0; p < P; ++p) {
+    const double *s = &sums[(size_t)p * sums_width];
+    double *pr = &h->profile[(size_t)p * 5];
+    const double expected_inventory = s[5] / total_n;
+    pr[0] = expected_inventory;
+    pr[1] = s[1] / total_n;
+    pr[2] = s[2] / total_n;
+    pr[3] = s[3] / total_n;
+    pr[4] = s[4] / total_n;
+    h->deltas[p] = (s[0] / h->forward_price[p] / total_n) * (h->discount_deltas ? h->settle_df[p] : 1.0);
+    double qbar[LSMC_MAX_BASIS];
+    for (int k = 0; k < K; ++k) qbar[k] = s[kForwardSums + k] / total_n;
+    trigger_prices_for_period(*h, p, expected_inventory, qbar, h->trigger[p]);
+    prog += fwd_step;
+    if (progress) progress(prog, user);
+    check_cancel();
+  }
+
+  // ---- terminal PV, NPV and standard error (LSV.cs:595-618)
+  double end_period_pv = 0.0;
+  const bool need_pv_host = !h->model->must_be_empty_at_end();
+  h->pv_by_sim.clear();
+  double npv, variance;
+  if (need_pv_host) {
+    if (h->comm.world() > 1) throw Error(LSMC_ERR_UNSUPPORTED, "Terminal inventory value with sharded paths is not supported yet.");
+    std::vector<double> pv(N), inv(N), s_end(N);
+    CUDA_OK(cudaMemcpy(pv.data(), h->pv.ptr, N * sizeof(double), cudaMemcpyDeviceToHost));
+    CUDA_OK(cudaMemcpy(inv.data(), h->final_inv.ptr, N * sizeof(double), cudaMemcpyDeviceToHost));
+    CUDA_OK(cudaMemcpy(s_end.data(), h->sims[0].spot + (size_t)(P - h->first_sim) * N, N * sizeof(double), cudaMemcpyDeviceToHost));  // regression sims
+    std::vector<double> last_row(h->panels[5].ptr ? N : 0);
+    double running = 0.0;
+    for (int64_t n = 0; n < N; ++n) {
+      const double t = h->model->terminal_npv(s_end[n], inv[n]);
+      running += t;
+      const double add = h->compat_terminal ? running : t;  // cumulative-sum quirk of LSV.cs:606-609
+      pv[n] += add;
+      if (!last_row.empty()) last_row[n] = add;
+    }
+    end_period_pv = running / N;
+    if (!last_row.empty()) CUDA_OK(cudaMemcpy(h->panels[5].ptr + (size_t)P * N, last_row.data(), N * sizeof(double), cudaMemcpyHostToDevice));
+    CUDA_OK(cudaMemcpy(h->pv.ptr, pv.data(), N * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  {
+    double sum = device_sum(h, h->pv.ptr, N, 0.0, 1);
+    h->comm.all_reduce_host(&sum, 1, st);
+    npv = sum / total_n;
+    double ss = device_sum(h, h->pv.ptr, N, npv, 2);
+    h->comm.all_reduce_host(&ss, 1, st);
+    variance = total_n > 1 ? ss / (total_n - 1.0) : 0.0;
+  }
+  double back_sum = device_sum(h, v_first, N, 0.0, 1);
+  h->comm.all_reduce_host(&back_sum, 1, st);
+  double final_inv_sum = device_sum(h, h->final_inv.ptr, N, 0.0, 1);
+  h->comm.all_reduce_host(&final_inv_sum, 1, st);
+
+  h->scalars.npv = npv;
+  h->scalars.std_error = std::sqrt(variance) / std::sqrt(total_n);
+  h->scalars.backward_npv = back_sum / total_n;
+  double *pr = &h->profile[(size_t)P * 5];  // LSV.cs:627-629
+  pr[0] = final_inv_sum / total_n;
+  pr[4] = end_period_pv;
+  h->scalars.ms_pseudo_inverse = t_pinv.ms();
+  h->scalars.ms_backward = t_back.ms() + h->scalars.ms_pseudo_inverse;
+  h->scalars.ms_forward = t_fwd.ms();
+  h->scalars.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+  h->has_results = true;
+  if (progress) progress(1.0, user);  // LSV.cs:644
+}
+
+}  // namespace
+
+// ================================================================================================ C ABI
+extern "C" {
+
+lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
+  if (!out) return LSMC_ERR_ARGUMENT;
+  *out = nullptr;
+  std::unique_ptr<lsmc_handle> h(new lsmc_handle);
+  try {
+    validate_problem(pb);
+    h->model.reset(new StorageModel(pb->storage));
+    h->N = pb->num_sims;
+    h->P = pb->storage.num_periods;
+    h->K = pb->num_basis;
+    h->F = pb->num_factors;
+    h->KP = padded_basis(h->K);
+    h->acc_k = acc_width(h->K);
+    h->current_active = pb->current_period_is_active != 0;
+    h->discount_deltas = pb->discount_deltas != 0;
+    h->compat_terminal = pb->reference_compat_terminal_pv != 0;
+    h->flags = pb->simulation_data_returned;
+    h->inventory = pb->inventory;
+    h->tolerance = pb->numerical_tolerance;
+    h->grid_spacing = pb->grid_spacing;
+    h->extra = pb->extra_decisions;
+    h->forward_price.assign(pb->forward_price, pb->forward_price + h->P + 1);
+    h->settle_df.assign(pb->settle_df, pb->settle_df + h->P);
+    h->powers.assign(pb->basis_powers, pb->basis_powers + (size_t)h->K * (1 + h->F));
+    h->tables = build_tables(*h->model, *pb);  // inventory space, grids, decision sets: all validation happens here
+    h->first_sim = h->current_active ? 1 : 0;
+    h->sim_rows = h->P + 1 - h->first_sim;
+    h->Gmax = h->tables.max_grid;
+    h->D = h->tables.max_decisions;
+    h->pitch = (h->N + 31) / 32 * 32;
+    h->device = device;
+
+    require_device(device);
+    CUDA_OK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    h->v_a.allocate((size_t)h->Gmax * h->pitch);
+    h->v_b.allocate((size_t)h->Gmax * h->pitch);
+    h->gamma.allocate((size_t)h->P * h->Gmax * h->K);
+    h->rinv.allocate((size_t)h->P * h->K * h->K * 2);
+    CUDA_OK(cudaMemset(h->rinv.ptr, 0, h->rinv.count * sizeof(double)));
+    const int64_t num_tiles = (h->N + kTilePaths - 1) / kTilePaths;
+    h->partials.allocate((size_t)num_tiles * h->Gmax * h->acc_k);
+    h->pv.allocate(h->N);
+    h->final_inv.allocate(h->N);
+    h->error_flag.allocate(1);
+    h->block_sums.allocate(512);
+    const uint32_t panel_flags[6] = {LSMC_RETURN_INVENTORY, LSMC_RETURN_INJECT_WITHDRAW_VOLUME, LSMC_RETURN_CMDTY_CONSUMED,
+                                     LSMC_RETURN_INVENTORY_LOSS, LSMC_RETURN_NET_VOLUME, LSMC_RETURN_PV};
+    for (int i = 0; i < 6; ++i)
+      if (h->flags & panel_flags[i]) {
+        h->panels[i].allocate((size_t)(h->P + 1) * h->N);
+        CUDA_OK(cudaMemset(h->panels[i].ptr, 0, h->panels[i].count * sizeof(double)));
+      }
+    if (h->flags & LSMC_RETURN_DECISION_INDEX) h->panels[6].allocate((size_t)h->P * h->N);
+    build_device_tables(h.get());
+    *out = h.release();
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(nullptr, e);
+  }
+}
+
+static lsmc_status set_sims_impl(lsmc_handle *h, int which, const double *spot, const double *const *factors, bool device_ptrs) {
+  if (!h) return LSMC_ERR_ARGUMENT;
+  try {
+    if (which != 0 && which != 1) throw Error(LSMC_ERR_ARGUMENT, "which must be 0 (regression) or 1 (valuation)");
+    if (!spot || (h->F > 0 && !factors)) throw Error(LSMC_ERR_ARGUMENT, which == 0 ? "regressionSpotSim is null" : "valuationSpotSim is null");
+    CUDA_OK(cudaSetDevice(h->device));
+    SimSet &s = h->sims[which];
+    const size_t count = (size_t)h->sim_rows * h->N;
+    if (device_ptrs) {
+      s.spot = spot;
+      for (int i = 0; i < h->F; ++i) s.factors[i] = factors[i];
+    } else {
+      s.owned_spot.allocate(count);
+      CUDA_OK(cudaMemcpyAsync(s.owned_spot.ptr, spot, count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      s.spot = s.owned_spot.ptr;
+      for (int i = 0; i < h->F; ++i) {
+        if (!factors[i]) throw Error(LSMC_ERR_ARGUMENT, "a factor simulation panel is null");
+        s.owned_factors[i].allocate(count);
+        CUDA_OK(cudaMemcpyAsync(s.owned_factors[i].ptr, factors[i], count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        s.factors[i] = s.owned_factors[i].ptr;
+      }
+      CUDA_OK(cudaStreamSynchronize(h->stream));
+    }
+    s.ms_simulation = 0.0;
+    s.ready = true;
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
+lsmc_status lsmc_set_sims(lsmc_handle *h, int which, const double *spot, const double *const *factors) {
+  return set_sims_impl(h, which, spot, factors, false);
+}
+
+lsmc_status lsmc_set_sims_device(lsmc_handle *h, int which, const double *spot, const double *const *factors) {
+  return set_sims_impl(h, which, spot, factors, true);
+}
+
+lsmc_status lsmc_simulate(lsmc_handle *h, int which, const lsmc_multi_factor_params *params, uint64_t seed, int antithetic,
+                          int64_t first_path_id) {
+  if (!h) return LSMC_ERR_ARGUMENT;
+  try {
+    if (which != 0 && which != 1) throw Error(LSMC_ERR_ARGUMENT, "which must be 0 (regression) or 1 (valuation)");
+    if (!params) throw Error(LSMC_ERR_ARGUMENT, "modelParameters is null");
+    if (params->num_factors != h->F) throw Error(LSMC_ERR_ARGUMENT, "model has a different number of factors than the problem");
+    CUDA_OK(cudaSetDevice(h->device));
+    SimSet &s = h->sims[which];
+    const size_t count = (size_t)h->sim_rows * h->N;
+    s.owned_spot.allocate(count);
+    double *fac[LSMC_MAX_FACTORS] = {};
+    for (int i = 0; i < h->F; ++i) {
+      s.owned_factors[i].allocate(count);
+      fac[i] = s.owned_factors[i].ptr;
+    }
+    Timer t(h->stream);
+    t.start();
+    simulate_multi_factor(*params, h->P, h->first_sim, h->forward_price.data(), h->N, seed, antithetic != 0, first_path_id,
+                          s.owned_spot.ptr, fac, h->stream);
+    t.stop();
+    CUDA_OK(cudaStreamSynchronize(h->stream));
+    CUDA_OK(cudaGetLastError());
+    s.ms_simulation = t.ms();
+    s.spot = s.owned_spot.ptr;
+    for (int i = 0; i < h->F; ++i) s.factors[i] = fac[i];
+    s.ready = true;
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
+lsmc_status lsmc_run(lsmc_handle *h, lsmc_progress_fn progress, void *user, const volatile int *cancel) {
+  if (!h) return LSMC_ERR_ARGUMENT;
+  try {
+    run_valuation(h, progress, user, cancel);
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
+int32_t lsmc_num_sim_periods(const lsmc_handle *h) { return h ? h->sim_rows : 0; }
+int32_t lsmc_num_periods(const lsmc_handle *h) { return h ? h->P : 0; }
+int32_t lsmc_max_grid_points(const lsmc_handle *h) { return h ? h->Gmax : 0; }
+int64_t lsmc_num_evaluations(const lsmc_handle *h) { return h ? h->tables.grid_point_steps * h->N : 0; }
+
+int32_t lsmc_get_grid(const lsmc_handle *h, int32_t period, double *out, int32_t capacity) {
+  if (!h || period < 0 || period > h->P) return 0;
+  const std::vector<double> &g = h->tables.periods[period].grid;
+  for (int i = 0; i < std::min<int>(capacity, (int)g.size()); ++i) out[i] = g[i];
+  return (int32_t)g.size();
+}
+
+lsmc_status lsmc_get_results(lsmc_handle *h, lsmc_results *out) {
+  if (!h || !out) return LSMC_ERR_ARGUMENT;
+  try {
+    if (!h->has_results) throw Error(LSMC_ERR_INVALID_OPERATION, "lsmc_run has not completed on this handle.");
+    double *deltas = out->deltas, *profile = out->profile, *pv = out->pv_by_sim;
+    lsmc_trigger_prices *trig = out->trigger_prices;
+    *out = h->scalars;
+    out->deltas = deltas;
+    out->profile = profile;
+    out->trigger_prices = trig;
+    out->pv_by_sim = pv;
+    if (deltas) std::copy(h->deltas.begin(), h->deltas.end(), deltas);
+    if (profile) std::copy(h->profile.begin(), h->profile.end(), profile);
+    if (trig) std::copy(h->trigger.begin(), h->trigger.end(), trig);
+    if (pv) {
+      CUDA_OK(cudaSetDevice(h->device));
+      CUDA_OK(cudaMemcpy(pv, h->pv.ptr, h->N * sizeof(double), cudaMemcpyDeviceToHost));
+    }
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
+lsmc_status lsmc_copy_panel(lsmc_handle *h, lsmc_panel which, double *dst) {
+  if (!h || !dst) return LSMC_ERR_ARGUMENT;
+  try {
+    if (!h->has_results) throw Error(LSMC_ERR_INVALID_OPERATION, "lsmc_run has not completed on this handle.");
+    CUDA_OK(cudaSetDevice(h->device));
+    const size_t N = h->N;
+    auto copy = [&](const double *src, size_t count) {
+      if (!src) throw Error(LSMC_ERR_INVALID_OPERATION, "This panel was not requested in SimulationDataReturned.");
+      CUDA_OK(cudaMemcpy(dst, src, count * sizeof(double), cudaMemcpyDeviceToHost));
+    };
+    switch (which) {
+      case LSMC_PANEL_INVENTORY: copy(h->panels[0].ptr, (h->P + 1) * N); break;
+      case LSMC_PANEL_INJECT_WITHDRAW_VOLUME: copy(h->panels[1].ptr, (h->P + 1) * N); break;
+      case LSMC_PANEL_CMDTY_CONSUMED: copy(h->panels[2].ptr, (h->P + 1) * N); break;
+      case LSMC_PANEL_INVENTORY_LOSS: copy(h->panels[3].ptr, (h->P + 1) * N); break;
+      case LSMC_PANEL_NET_VOLUME: copy(h->panels[4].ptr, (h->P + 1) * N); break;
+      case LSMC_PANEL_PV: copy(h->panels[5].ptr, (h->P + 1) * N); break;
+      case LSMC_PANEL_DECISION_INDEX: copy(h->panels[6].ptr, (size_t)h->P * N); break;
+      case LSMC_PANEL_SPOT_REGRESSION: copy(h->sims[0].spot, (size_t)h->sim_rows * N); break;
+      case LSMC_PANEL_SPOT_VALUATION: copy(h->sims[1].spot, (size_t)h->sim_rows * N); break;
+      case LSMC_PANEL_FACTORS_REGRESSION:
+      case LSMC_PANEL_FACTORS_VALUATION: {
+        const SimSet &s = h->sims[which == LSMC_PANEL_FACTORS_REGRESSION ? 0 : 1];
+        for (int i = 0; i < h->F; ++i)
+          CUDA_OK(cudaMemcpy(dst + (size_t)i * h->sim_rows * N, s.factors[i], (size_t)h->sim_rows * N * sizeof(double), cudaMemcpyDeviceToHost));
+        break;
+      }
+      default: throw Error(LSMC_ERR_ARGUMENT, "unknown panel");
+    }
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
+lsmc_status lsmc_get_regression(lsmc_handle *h, double *gamma, double *r_inverse) {
+  if (!h) return LSMC_ERR_ARGUMENT;
+  try {
+    if (!h->has_results) throw Error(LSMC_ERR_INVALID_OPERATION, "lsmc_run has not completed on this handle.");
+    if (gamma) std::copy(h->h_gamma.begin(), h->h_gamma.end(), gamma);
+    if (r_inverse)
+      for (size_t i = 0; i < h->h_rinv.size() / 2; ++i) r_inverse[i] = h->h_rinv[2 * i];
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
+const char *lsmc_last_error(const lsmc_handle *h) { return h ? h->error.c_str() : g_create_error.c_str(); }
+
+void lsmc_destroy(lsmc_handle *h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) {
+    cudaStreamSynchronize(h->stream);
+    cudaStreamDestroy(h->stream);
+  }
+  delete h;
+}
+
+lsmc_status lsmc_comm_unique_id(void *id_out) {
+  try {
+    Comm::unique_id(id_out);
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(nullptr, e);
+  }
+}
+
+lsmc_status lsmc_comm_init(lsmc_handle *h, const void *id, int rank, int world, int64_t total_sims) {
+  if (!h) return LSMC_ERR_ARGUMENT;
+  try {
+    CUDA_OK(cudaSetDevice(h->device));
+    h->comm.init(id, rank, world, total_sims);
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
+// ---- host helpers -----------------------------------------------------------------------------------------------
+lsmc_status lsmc_calculate_inventory_space(const lsmc_storage *storage, double starting_inventory, double *out_min, double *out_max) {
+  try {
+    if (!storage) throw Error(LSMC_ERR_ARGUMENT, "storage is null");
+    StorageModel st(*storage);
+    std::vector<double> lo, hi;
+    calculate_inventory_space(st, starting_inventory, lo, hi);
+    std::copy(lo.begin(), lo.end(), out_min);
+    std::copy(hi.begin(), hi.end(), out_max);
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(nullptr, e);
+  }
+}
+
+int32_t lsmc_bang_bang_decision_set(double min_rate, double max_rate, double inventory, double inventory_loss, double next_min,
+                                    double next_max, double tolerance, int32_t extra, double *out) {
+  try {
+    double tmp[LSMC_MAX_DECISIONS];
+    int n = bang_bang_decision_set({min_rate, max_rate}, inventory, inventory_loss, next_min, next_max, tolerance, extra, tmp);
+    std::copy(tmp, tmp + n, out);
+    return n;
+  } catch (const std::exception &e) {
+    return -status_of(nullptr, e);
+  }
+}
+
+lsmc_status lsmc_bisect_inventory_space(const double *grid, int32_t n, double inventory, double tolerance, int32_t *lower, int32_t *upper) {
+  try {
+    int lo, hi;
+    bisect_inventory_space(grid, n, inventory, tolerance, &lo, &hi);
+    *lower = lo;
+    *upper = hi;
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(nullptr, e);
+  }
+}
+
+int32_t lsmc_grid_points(double lower, double upper, double spacing, double *out, int32_t capacity) {
+  try {
+    std::vector<double> g = grid_points(lower, upper, spacing);
+    for (int i = 0; i < std::min<int>(capacity, (int)g.size()); ++i) out[i] = g[i];
+    return (int32_t)g.size();
+  } catch (const std::exception &e) {
+    return -status_of(nullptr, e);
+  }
+}
+
+lsmc_status lsmc_inject_withdraw_range(const lsmc_storage *storage, int32_t period, double inventory, double *min_rate, double *max_rate) {
+  try {
+    if (!storage) throw Error(LSMC_ERR_ARGUMENT, "storage is null");
+    StorageModel st(*storage);
+    RateRange r = st.inject_withdraw_range(period, inventory);
+    *min_rate = r.lo;
+    *max_rate = r.hi;
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(nullptr, e);
+  }
+}
+
+lsmc_status lsmc_inventory_space_bounds(const lsmc_storage *storage, int32_t period, double next_lower, double next_upper,
+                                        double *lower, double *upper) {
+  try {
+    if (!storage) throw Error(LSMC_ERR_ARGUMENT, "storage is null");
+    StorageModel st(*storage);
+    if (period < 0 || period >= st.num_periods()) throw Error(LSMC_ERR_ARGUMENT, "period out of range");
+    *upper = st.space_upper_bound(period, next_lower, next_upper);
+    *lower = st.space_lower_bound(period, next_lower, next_upper);
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(nullptr, e);
+  }
+}
+
+int32_t lsmc_parse_basis(const char *expression, int32_t num_factors, int32_t *powers, int32_t capacity) {
+  try {
+    return parse_basis(expression, num_factors, powers, capacity);
+  } catch (const std::exception &e) {
+    return -status_of(nullptr, e);
+  }
+}
+
+}  // extern "C"
