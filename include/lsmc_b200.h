@@ -184,6 +184,12 @@ typedef struct lsmc_results {
   /* Stopwatches.cs:35-80 buckets, milliseconds (device time for GPU phases). */
   double ms_total, ms_regression_sim, ms_valuation_sim, ms_backward, ms_pseudo_inverse, ms_forward;
   int64_t kernel_launches; /* kernels of this library launched by the last lsmc_run */
+  /* Device time (CUDA events on the launching stream) of the dominant kernel, the fused backward-induction step, summed
+     over its launches of the last run, and the number of those launches; ms_device is the event time from the first
+     to the last kernel of the run. */
+  double ms_backward_kernel;
+  int64_t backward_kernel_launches;
+  double ms_device;
 } lsmc_results;
 
 /* Per-sim panels selectable with SimulationDataReturned (LSV.cs:356-366,636-643). */

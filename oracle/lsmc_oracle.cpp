@@ -1188,6 +1188,16 @@ int oracle_lsmc_calculate(const lsmc_problem *pb, const double *reg_spot, const 
       try {
         double price = prices[n];
         double inventory = inv_this[n];
+        // DEPARTURE from the reference (documented in DESIGN.md, "rounding at the inventory limits"): inv + v - loss can land
+        // a few ulps outside [MinInventory, MaxInventory] when a decision was constrained to hit the limit and the
+        // period has an inventory loss; CmdtyStorage.GetInjectWithdrawRange (CS.cs:88-94) would then throw.  A breach
+        // smaller than NumericalTolerance is snapped onto the limit instead (same rule in the CUDA forward kernel).
+        {
+          double lo = st.min_inventory(p), hi = st.max_inventory(p);
+          if (inventory < lo && lo - inventory <= tol) inventory = lo;
+          if (inventory > hi && inventory - hi <= tol) inventory = hi;
+          inv_this[n] = inventory;
+        }
         Range range = st.inject_withdraw_range(p, inventory);
         double inventory_loss = st.loss_pct(p) * inventory;
         std::vector<double> decisions = bang_bang_decision_set(range, inventory, inventory_loss, next_min, next_max, tol, extra);

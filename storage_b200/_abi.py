@@ -22,6 +22,8 @@ LSMC_COMM_ID_BYTES = 128
  LSMC_PANEL_NET_VOLUME, LSMC_PANEL_PV, LSMC_PANEL_SPOT_REGRESSION, LSMC_PANEL_SPOT_VALUATION,
  LSMC_PANEL_FACTORS_REGRESSION, LSMC_PANEL_FACTORS_VALUATION, LSMC_PANEL_DECISION_INDEX) = range(11)
 
+LSMC_RETURN_DECISION_INDEX = 1 << 16
+
 c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)
 
@@ -118,6 +120,9 @@ class lsmc_results(C.Structure):
         ("ms_pseudo_inverse", C.c_double),
         ("ms_forward", C.c_double),
         ("kernel_launches", C.c_int64),
+        ("ms_backward_kernel", C.c_double),
+        ("backward_kernel_launches", C.c_int64),
+        ("ms_device", C.c_double),
     ]
 
 

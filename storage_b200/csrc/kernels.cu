@@ -603,7 +603,10 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
       double q[KP];
       eval_q<KP>(b, s_pw, s_rinv, K, F, nc, valid, q);
 
-      // LSV.cs:445-508 for this path
+      // LSV.cs:445-508 for this path.  A breach of the inventory limits smaller than NumericalTolerance (rounding of
+      // inv + v - loss after a constrained decision) is snapped onto the limit; the reference would throw (CS.cs:88-94).
+      if (inventory < pp.min_inventory && pp.min_inventory - inventory <= a.tolerance) inventory = pp.min_inventory;
+      if (inventory > pp.max_inventory && inventory - pp.max_inventory <= a.tolerance) inventory = pp.max_inventory;
       DevRange range = storage_range_dev(a, pp, inventory, &err);
       const double loss = pp.loss * inventory;
       double decisions[LSMC_MAX_DECISIONS];

@@ -373,7 +373,18 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   };
   check_cancel();
 
-  Timer t_pinv(st), t_back(st), t_fwd(st);
+  Timer t_pinv(st), t_back(st), t_fwd(st), t_dev(st);
+  struct EventList {
+    std::vector<cudaEvent_t> ev;
+    explicit EventList(size_t n) : ev(n) {
+      for (auto &e : ev) cudaEventCreate(&e);
+    }
+    ~EventList() {
+      for (auto &e : ev) cudaEventDestroy(e);
+    }
+    cudaEvent_t &operator[](size_t i) { return ev[i]; }
+  } step_events(2 * (size_t)P);
+  t_dev.start();
   // ---- regression pre-pass: Gram matrices, Cholesky factors and R^-1 of every regression period (LSV.cs:191-196)
   const int first_reg = h->current_active ? 1 : 0;
   const int num_slots = P - first_reg;
@@ -462,7 +473,9 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     int tiles_per_chunk = (int)std::max<int64_t>(1, std::min<int64_t>(16, num_tiles / want_chunks));
     const int num_chunks = (int)((num_tiles + tiles_per_chunk - 1) / tiles_per_chunk);
     a.tiles_per_chunk = tiles_per_chunk;
+    if (!terminal) cudaEventRecord(step_events[2 * p], st);
     launch_backward_step(a, num_chunks, st);
+    if (!terminal) cudaEventRecord(step_events[2 * p + 1], st);
     launches++;
     return num_chunks;
   };
@@ -517,8 +530,8 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   t_fwd.start();
   const int sums_width = kForwardSums + K;
   const int fwd_ctas = (int)std::min<int64_t>((N + kThreads - 1) / kThreads, (int64_t)sm_count * 8);
-  h->step_sums.allocate((size_t)P * fwd_ctas * sums_width);
-  h->step_totals.allocate((size_t)P * sums_width);
+  if (h->step_sums.count < (size_t)P * fwd_ctas * sums_width) h->step_sums.allocate((size_t)P * fwd_ctas * sums_width);
+  if (h->step_totals.count < (size_t)P * sums_width) h->step_totals.allocate((size_t)P * sums_width);
   ForwardArgs fa{};
   fa.N = N;
   fa.P = P;
@@ -558,6 +571,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   launch_reduce_step_sums(h->step_sums.ptr, P, fwd_ctas, sums_width, h->step_totals.ptr, st);
   launches++;
   t_fwd.stop();
+  t_dev.stop();
 
   std::vector<double> sums((size_t)P * sums_width);
   CUDA_OK(cudaMemcpyAsync(sums.data(), h->step_totals.ptr, sums.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -645,6 +659,17 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   h->scalars.ms_pseudo_inverse = t_pinv.ms();
   h->scalars.ms_backward = t_back.ms() + h->scalars.ms_pseudo_inverse;
   h->scalars.ms_forward = t_fwd.ms();
+  h->scalars.ms_device = t_dev.ms();
+  {
+    double total = 0.0;
+    for (int p = 0; p < P; ++p) {
+      float m = 0.f;
+      cudaEventElapsedTime(&m, step_events[2 * p], step_events[2 * p + 1]);
+      total += m;
+    }
+    h->scalars.ms_backward_kernel = total;
+    h->scalars.backward_kernel_launches = P;
+  }
   h->scalars.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
   h->has_results = true;
   if (progress) progress(1.0, user);  // LSV.cs:644

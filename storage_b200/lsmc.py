@@ -407,7 +407,7 @@ class LsmcValuationParameters:
 class FlatProblem:
     """lsmc_problem descriptor + the numpy arrays that back its pointers."""
 
-    def __init__(self, params, num_sims, num_factors):
+    def __init__(self, params, num_sims, num_factors, extra_flags=0):
         st = params.Storage
         cur = params.CurrentPeriod
         start_active = max(st.StartPeriod, cur)
@@ -439,7 +439,7 @@ class FlatProblem:
         pb.numerical_tolerance = params.NumericalTolerance
         pb.extra_decisions = params.ExtraDecisions
         pb.discount_deltas = 1 if params.DiscountDeltas else 0
-        pb.simulation_data_returned = int(params.SimulationDataReturned)
+        pb.simulation_data_returned = int(params.SimulationDataReturned) | int(extra_flags)
         pb.num_factors = num_factors
         pb.num_basis = self.powers.shape[0]
         pb.basis_powers = self.powers.ctypes.data_as(_abi.c_int32_p)
@@ -610,7 +610,7 @@ class LsmcStorageValuation:
         else:
             model, num_sims = spec[1], spec[2]
             num_factors = model.NumFactors
-        flat = FlatProblem(p, num_sims, num_factors)
+        flat = FlatProblem(p, num_sims, num_factors, extra_flags=_abi.LSMC_RETURN_DECISION_INDEX if keep_decisions else 0)
         h = Handle(flat, self._device)
         try:
             lib = h.lib
@@ -669,6 +669,9 @@ class LsmcStorageValuation:
         out.PvBySim = pv
         out.Timings = {k: getattr(r, "ms_" + k) for k in ("total", "regression_sim", "valuation_sim", "backward", "pseudo_inverse", "forward")}
         out.KernelLaunches = r.kernel_launches
+        out.Timings["backward_kernel"] = r.ms_backward_kernel
+        out.Timings["device"] = r.ms_device
+        out.BackwardKernelLaunches = r.backward_kernel_launches
         flags = p.SimulationDataReturned
         S = SimulationDataReturned
         rows = len(flat.sim_periods)

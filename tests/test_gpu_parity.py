@@ -1,0 +1,127 @@
+"""GPU parity: the CUDA path (through the C ABI / host API mirror) against the CPU oracle on identical pre-simulated paths
+fed through the caller-supplied-simulation overload (north star).
+
+Tolerances (BASELINE.json north_star): NPV, deltas, profile within 1e-9 relative in FP64; argmax decisions identical.
+"Identical decisions" is checked on decision *volumes*: when the inventory-space bound makes two entries of a decision set
+coincide to ~1e-12 (e.g. max-rate withdrawal vs withdrawal constrained by the next step's maximum inventory) the index of
+the maximum is decided by the last ulp of the continuation value, so index flips between numerically identical decisions
+are reported but not counted as mismatches.
+"""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from storage_b200 import SimulationDataReturned
+from tests import cases
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-9
+
+
+def material_mismatches(gpu, ref):
+    idx_diff = gpu.DecisionIndexBySim != ref.decision_index
+    vol_diff = np.abs(gpu.InjectWithdrawVolumeBySim[:-1] - ref.inject_withdraw_volume[:-1]) > 1e-6
+    return int(np.count_nonzero(idx_diff)), int(np.count_nonzero(vol_diff))
+
+
+def check_case(case, rel=REL):
+    case.params.SimulationDataReturned = SimulationDataReturned.All
+    gpu = cases.run_gpu(case)
+    ref = oracle.lsmc_calculate(case.flat, case.reg_spot, case.reg_factors, case.val_spot, case.val_factors, mode=1)
+    raw, material = material_mismatches(gpu, ref)
+    assert material == 0, f"{material} material decision mismatches ({raw} raw index flips)"
+    assert gpu.Npv == pytest.approx(ref.npv, rel=rel)
+    assert gpu.ValuationSimStandardError == pytest.approx(ref.std_error, rel=1e-8)
+    assert gpu.BackwardNpv == pytest.approx(ref.backward_npv, rel=rel)
+    P = case.flat.num_periods
+    periods = case.flat.periods
+    deltas = np.array([gpu.Deltas[p] for p in periods])
+    scale = np.abs(ref.deltas).max() + 1e-300
+    assert np.abs(deltas - ref.deltas).max() <= rel * scale
+    prof = np.array([[sp.Inventory, sp.InjectWithdrawVolume, sp.CmdtyConsumed, sp.InventoryLoss, sp.PeriodPv]
+                     for sp in (gpu.ExpectedStorageProfile[p] for p in periods)])
+    for col in range(5):
+        s = np.abs(ref.profile[:, col]).max() + 1e-300
+        assert np.abs(prof[:, col] - ref.profile[:, col]).max() <= rel * s, f"profile column {col}"
+    # per-sim panels
+    np.testing.assert_allclose(gpu.PvBySim, ref.pv_by_sim, rtol=1e-9, atol=1e-6)
+    np.testing.assert_allclose(gpu.InventoryBySim, ref.inventory, rtol=1e-9, atol=1e-6)
+    np.testing.assert_allclose(gpu.InjectWithdrawVolumeBySim, ref.inject_withdraw_volume, rtol=1e-9, atol=1e-6)
+    np.testing.assert_allclose(gpu.CmdtyConsumedBySim, ref.cmdty_consumed, rtol=1e-9, atol=1e-6)
+    np.testing.assert_allclose(gpu.InventoryLossBySim, ref.inventory_loss, rtol=1e-9, atol=1e-6)
+    np.testing.assert_allclose(gpu.NetVolumeBySim, ref.net_volume, rtol=1e-9, atol=1e-6)
+    np.testing.assert_allclose(gpu.PvByPeriodAndSim, ref.pv, rtol=1e-9, atol=1e-5)
+    # trigger prices
+    for i in range(P):
+        t_gpu, t_ref = gpu.TriggerPriceVolumeProfiles[periods[i]], ref.trigger[i]
+        assert len(t_gpu.InjectTriggerPrices) == t_ref.num_inject and len(t_gpu.WithdrawTriggerPrices) == t_ref.num_withdraw
+        for j, (vol, price) in enumerate(t_gpu.InjectTriggerPrices):
+            assert vol == pytest.approx(t_ref.inject_volume[j], rel=1e-9, abs=1e-9)
+            assert price == pytest.approx(t_ref.inject_price[j], rel=1e-7, abs=1e-7)
+        for j, (vol, price) in enumerate(t_gpu.WithdrawTriggerPrices):
+            assert vol == pytest.approx(t_ref.withdraw_volume[j], rel=1e-9, abs=1e-9)
+            assert price == pytest.approx(t_ref.withdraw_price[j], rel=1e-7, abs=1e-7)
+    return gpu, ref
+
+
+def test_config0_one_factor_cubic_basis():
+    """BASELINE.json configs[0] shape (2,000 paths, basis 1+s+s^2+s^3), 60 daily steps."""
+    check_case(cases.simple_one_factor(num_sims=2000, num_days=60, seed=11))
+
+
+def test_config0_full_year():
+    """configs[0] at its full size: 365 daily steps, 2,000 paths, 100-point grid."""
+    check_case(cases.simple_one_factor(num_sims=2000, num_days=365, seed=7, val_offset=-1))
+
+
+def test_valuation_date_inside_active_period():
+    """CurrentPeriod >= StartPeriod: period 0 uses the forward price and the sample-mean continuation (LSV.cs:174-185)."""
+    check_case(cases.simple_one_factor(num_sims=1500, num_days=45, seed=5, val_offset=12))
+
+
+def test_config1_three_factor_basis():
+    """configs[1] shape: 3-factor seasonal model, basis 1+x0+x0^2+x1+x2+x0*x1+s, piecewise-linear ratchets."""
+    check_case(cases.three_factor_ratchets(num_sims=3000, num_days=90, seed=11, outages=False))
+
+
+def test_config2_ratchets_outages_loss_costs():
+    """configs[2] shape: time- and inventory-varying ratchets, outages, inventory loss, consumed commodity, inventory cost."""
+    check_case(cases.three_factor_ratchets(num_sims=2000, num_days=120, seed=3))
+
+
+@pytest.mark.parametrize("kind", ["step", "poly"])
+def test_other_constraint_kinds(kind):
+    check_case(cases.three_factor_ratchets(num_sims=1000, num_days=50, seed=9, kind=kind))
+
+
+def test_terminal_inventory_value_and_cumulative_quirk():
+    """!MustBeEmptyAtEnd with TerminalStorageNpv = price*inventory - 999 (LsmcStorageValuationTest.cs:125), including the
+    reference's running-sum terminal PV (LSV.cs:606-609)."""
+    check_case(cases.simple_one_factor(num_sims=1000, num_days=40, seed=2, terminal=(-999.0, 0.0, 0.0, 1.0)))
+
+
+def test_extra_decisions_and_discounted_deltas():
+    check_case(cases.simple_one_factor(num_sims=1000, num_days=40, seed=4, extra_decisions=2, discount_deltas=True))
+
+
+def test_ragged_path_count():
+    """N not a multiple of the tile (odd, prime): tail handling of the double2 tiles."""
+    check_case(cases.simple_one_factor(num_sims=1009, num_days=30, seed=6))
+    check_case(cases.simple_one_factor(num_sims=7, num_days=10, seed=6, grid_points=20))
+
+
+def test_rank_deficient_design_matrix_is_reported():
+    """Fewer paths than basis functions: the reference's QR would produce non-finite coefficients; the library reports it."""
+    from storage_b200 import NumericalError
+    with pytest.raises(NumericalError):
+        cases.run_gpu(cases.simple_one_factor(num_sims=3, num_days=10, seed=6, grid_points=20))
+
+
+def test_single_period_storage():
+    check_case(cases.simple_one_factor(num_sims=500, num_days=1, seed=8, inventory=300.0))
+
+
+def test_larger_path_count_config1():
+    """configs[1] nearer its size: 20,000 paths (the oracle's exact mode needs ~10 s here)."""
+    check_case(cases.three_factor_ratchets(num_sims=20_000, num_days=60, seed=21, outages=False))
