@@ -29,12 +29,10 @@ struct BasisSpec {
 
 struct BackwardStepArgs {
   int64_t N;            // paths on this device
-  int64_t pitch;        // row pitch of the V buffers, in doubles
+  int64_t pitch;        // row pitch of the V and Q buffers, in doubles
   int G;                // grid points of this period
-  int Gn;               // grid points of the next period
   int D;                // max decisions (row width of the decision table)
   int K;                // basis functions
-  int F;                // factors
   const double *v_next; // [Gn][pitch]
   double *v_this;       // [G][pitch]
   const double *gamma;  // [Gn][K] regression coefficients (orthonormal basis) of v_next on this period's basis
@@ -44,13 +42,11 @@ struct BackwardStepArgs {
   const double *spot;   // [N] prices used for the immediate cash flow (NULL: use const_price)
   double const_price;   // forward price when the period is the current period
   double settle_df;
-  BasisSpec basis_this; // basis evaluating the continuation value of this period
-  BasisSpec basis_prev; // basis of period-1, against which v_this is accumulated (regression of the next backward step)
+  const double *q_this; // [K][pitch] orthonormal basis rows of this period (NULL: mean mode, q = e_0)
+  const double *q_prev; // [K][pitch] basis rows of period-1 for the regression sums (NULL with accumulate: mean mode)
   int accumulate;       // 0: no further regression (period 0)
-  double *partials;     // [num_chunks][G][accK] per-chunk sums of q_prev[k] * v_this[g]
-  int acc_k;            // kAccK or 16
-  int tiles_per_chunk;  // path tiles a CTA walks through
-  const int32_t *powers;  // [K][1+F]
+  double *partials;     // [num_tiles][G][acc] per-tile sums of q_prev[k] * v_this[g]
+  int subtiles_per_cta; // inventory-grid sub-tiles (of kMaxGridTile points) one CTA sweeps
   // terminal mode: v_this[g][n] = TerminalStorageNpv(spot[n], grid_this[g]) instead of the decision step
   int terminal_mode;
   const double *grid_this;  // [G]

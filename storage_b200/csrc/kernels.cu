@@ -30,31 +30,52 @@ constexpr unsigned kFullMask = 0xffffffffu;
 
 // ------------------------------------------------------------------------------------------------------------------
 // Orthonormalised basis row of one path: monomials X_k (BasisFunctions.Generic, BasisFunctions.cs:93-135; integer powers
-// correctly rounded, products in factor-index order) followed by q_j = sum_{l<=j} X_l * Rinv[l][j] in double-double.
+// correctly rounded, products in factor-index order) followed by q_j = sum_{l<=j} X_l * Rinv[l][j] accumulated with
+// compensated (twice-the-working-precision) summation.  Loops over factors are deliberately not unrolled: this code is
+// cold relative to the decision loop and must stay small in the instruction cache.
 // ------------------------------------------------------------------------------------------------------------------
+__device__ __noinline__ double monomial_value(const int32_t *__restrict__ row, int F, double s, const double *__restrict__ x) {
+  double m = 1.0;
+  const int p0 = row[0];
+  if (p0 > 0) m = pow_int_rounded(s, p0);
+#pragma unroll 1
+  for (int i = 0; i < F; ++i) {
+    const int pi = row[1 + i];
+    if (pi > 0) m = m * pow_int_rounded(x[i], pi);
+  }
+  return m;
+}
+
 template <int KP>
 __device__ __forceinline__ void eval_monomials(const BasisSpec &b, const int32_t *__restrict__ pw, int K, int F, int64_t n,
                                                double (&X)[KP]) {
   const double s = b.spot[n];
   double x[LSMC_MAX_FACTORS];
+#pragma unroll 1
+  for (int i = 0; i < F; ++i) x[i] = b.factors[i][n];
 #pragma unroll
-  for (int i = 0; i < LSMC_MAX_FACTORS; ++i) x[i] = (i < F) ? b.factors[i][n] : 0.0;
+  for (int k = 0; k < KP; ++k) X[k] = (k < K) ? monomial_value(pw + k * (1 + F), F, s, x) : 0.0;
+}
+
+// q_j = sum_{l<=j} X_l * (R.hi + R.lo)[l][j]: error-free products, cascaded (Dot2) summation, one final rounding
+template <int KP>
+__device__ __forceinline__ void orthonormalise(const double (&X)[KP], const dd *__restrict__ rinv, int K, double (&q)[KP]) {
 #pragma unroll
-  for (int k = 0; k < KP; ++k) {
-    double m = 1.0;
-    if (k < K) {
-      const int32_t *row = pw + k * (1 + F);
-      const int p0 = row[0];
-      if (p0 > 0) m = pow_int_rounded(s, p0);
+  for (int j = 0; j < KP; ++j) {
+    double acc = 0.0, comp = 0.0;
+    if (j < K) {
 #pragma unroll
-      for (int i = 0; i < LSMC_MAX_FACTORS; ++i) {
-        if (i < F) {
-          const int pi = row[1 + i];
-          if (pi > 0) m = m * pow_int_rounded(x[i], pi);
-        }
+      for (int l = 0; l <= j; ++l) {
+        const dd r = rinv[l * K + j];
+        const double p = X[l] * r.hi;
+        const double e = __fma_rn(X[l], r.hi, -p);
+        const double s = acc + p;
+        const double bb = s - acc;
+        comp += ((acc - (s - bb)) + (p - bb)) + __fma_rn(X[l], r.lo, e);
+        acc = s;
       }
     }
-    X[k] = m;
+    q[j] = acc + comp;
   }
 }
 
@@ -70,15 +91,7 @@ __device__ __forceinline__ void eval_q(const BasisSpec &b, const int32_t *__rest
   }
   double X[KP];
   eval_monomials<KP>(b, pw, K, F, n, X);
-#pragma unroll
-  for (int j = 0; j < KP; ++j) {
-    if (j < K) {
-      dd acc{0.0, 0.0};
-#pragma unroll
-      for (int l = 0; l <= j; ++l) acc = dd_add(acc, dd_mul_d(rinv[l * K + j], X[l]));
-      q[j] = acc.hi;
-    }
-  }
+  orthonormalise<KP>(X, rinv, K, q);
 }
 
 // Sum of 8 per-lane values over the warp with 9 shuffles: after the call every lane holds the warp total of component
@@ -132,9 +145,10 @@ __global__ void __launch_bounds__(kThreads) gram_kernel(GramArgs a) {
   const int K = a.K, F = a.F;
   for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
   __syncthreads();
-  dd acc[NP];
+  // compensated accumulation: hi carries the running sum, lo collects the rounding errors of the sums and products
+  double hi[NP], lo[NP];
 #pragma unroll
-  for (int i = 0; i < NP; ++i) acc[i] = dd{0.0, 0.0};
+  for (int i = 0; i < NP; ++i) hi[i] = lo[i] = 0.0;
   const int64_t begin = (int64_t)blockIdx.x * a.chunk_paths;
   const int64_t end = min(begin + a.chunk_paths, a.N);
   for (int64_t n = begin + threadIdx.x; n < end; n += blockDim.x) {
@@ -144,13 +158,19 @@ __global__ void __launch_bounds__(kThreads) gram_kernel(GramArgs a) {
 #pragma unroll
     for (int i = 0; i < KP; ++i)
 #pragma unroll
-      for (int j = i; j < KP; ++j, ++idx)
-        if (j < K) acc[idx] = dd_add(acc[idx], two_prod(X[i], X[j]));
+      for (int j = i; j < KP; ++j, ++idx) {
+        const double p = X[i] * X[j];
+        const double e = __fma_rn(X[i], X[j], -p);
+        const double s = hi[idx] + p;
+        const double bb = s - hi[idx];
+        lo[idx] += ((hi[idx] - (s - bb)) + (p - bb)) + e;
+        hi[idx] = s;
+      }
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int i = 0; i < NP; ++i) {
-    dd r = warp_reduce_dd(acc[i]);
+    dd r = warp_reduce_dd(quick_two_sum(hi[i], lo[i]));
     if (lane == 0) s_red[warp][i] = r;
   }
   __syncthreads();
@@ -226,150 +246,156 @@ __global__ void cholesky_kernel(CholeskyArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// Backward induction step
+// Orthonormal basis rows of one period, materialised once: Q[k][n] for the regression simulations.  32 B read and 8K B
+// written per path; the backward kernel then reads the rows of period p (continuation values) and p-1 (regression sums)
+// as coalesced double2 instead of re-deriving them per inventory-grid tile.
 // ------------------------------------------------------------------------------------------------------------------
-struct BackwardSmem {
-  // carved from dynamic shared memory by the kernel; sizes depend on D, K, acc_k
-  DevDecision *dec;     // [TG][D]
-  double *coef;         // [TG][D][KP]
-  double *inv_cost;     // [TG]
-  int32_t *nd;          // [TG]
-  dd *rinv_this;        // [K*K]
-  dd *rinv_prev;        // [K*K]
-  int32_t *pw;          // [K*(1+F)]
-  double *acc;          // [kWarps][TG][acc_k]
-};
-
 template <int KP>
-__device__ __forceinline__ BackwardSmem carve_backward_smem(unsigned char *base, int D, int K, int F, int acc_k) {
-  BackwardSmem s;
-  size_t off = 0;
-  auto take = [&](size_t bytes) {
-    unsigned char *p = base + off;
-    off += (bytes + 15) & ~size_t(15);
-    return p;
-  };
-  s.dec = reinterpret_cast<DevDecision *>(take(sizeof(DevDecision) * kMaxGridTile * D));
-  s.coef = reinterpret_cast<double *>(take(sizeof(double) * kMaxGridTile * D * KP));
-  s.inv_cost = reinterpret_cast<double *>(take(sizeof(double) * kMaxGridTile));
-  s.nd = reinterpret_cast<int32_t *>(take(sizeof(int32_t) * kMaxGridTile));
-  s.rinv_this = reinterpret_cast<dd *>(take(sizeof(dd) * K * K));
-  s.rinv_prev = reinterpret_cast<dd *>(take(sizeof(dd) * K * K));
-  s.pw = reinterpret_cast<int32_t *>(take(sizeof(int32_t) * K * (1 + F)));
-  s.acc = reinterpret_cast<double *>(take(sizeof(double) * kWarps * kMaxGridTile * acc_k));
-  return s;
+__global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
+  __shared__ int32_t s_pw[LSMC_MAX_BASIS * (1 + LSMC_MAX_FACTORS)];
+  __shared__ dd s_rinv[LSMC_MAX_BASIS * LSMC_MAX_BASIS];
+  const int K = a.K, F = a.F;
+  for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
+  for (int i = threadIdx.x; i < K * K; i += blockDim.x) s_rinv[i] = dd{a.spec.rinv[2 * i], a.spec.rinv[2 * i + 1]};
+  __syncthreads();
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= a.N) return;
+  double q[KP];
+  eval_q<KP>(a.spec, s_pw, s_rinv, K, F, n, true, q);
+#pragma unroll
+  for (int k = 0; k < KP; ++k)
+    if (k < K) a.q_out[(size_t)k * a.pitch + n] = q[k];
 }
 
-// grid = (grid tiles, path chunks): grid tiles of one path chunk are adjacent in launch order, so the halo rows of
-// v_next that neighbouring tiles share are re-read from L2, not HBM.
+// ------------------------------------------------------------------------------------------------------------------
+// Backward induction step
+// ------------------------------------------------------------------------------------------------------------------
+// One CTA = one tile of 256 paths (128 threads x double2) x a contiguous range of inventory-grid sub-tiles.  Within the
+// CTA the grid points are swept in ascending order, so the rows of v_next a decision interpolates between are re-used
+// from L1 by the neighbouring grid points and each row comes from HBM once.
 template <int KP>
 __global__ void __launch_bounds__(kThreads) backward_step_kernel(BackwardStepArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int ACC = KP <= 8 ? 8 : 16;  // width of a stored partial-sum row
-  const int K = a.K, F = a.F, D = a.D, acc_k = ACC;
-  BackwardSmem s = carve_backward_smem<KP>(smem_raw, D, K, F, acc_k);
-  const int g0 = blockIdx.x * kMaxGridTile;
-  const int gcount = min(kMaxGridTile, a.G - g0);
-  const int chunk = blockIdx.y;
+  constexpr int TG = kMaxGridTile;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int K = a.K, D = a.D;
+  // dynamic smem: dec [TG][D] | coef [TG][D][KP] | inv_cost [TG] | nd [TG] | acc [kWarps][TG][ACC]
+  DevDecision *s_dec = reinterpret_cast<DevDecision *>(smem_raw);
+  double *s_coef = reinterpret_cast<double *>(s_dec + (size_t)TG * D);
+  double *s_inv_cost = s_coef + (size_t)TG * D * KP;
+  double *s_acc = s_inv_cost + TG;
+  int32_t *s_nd = reinterpret_cast<int32_t *>(s_acc + (size_t)kWarps * TG * ACC);
+
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t tile = blockIdx.y;
+  const int64_t n0 = tile * kTilePaths + (int64_t)threadIdx.x * kPathsPerThread;
+  const bool valid0 = n0 < a.N, valid1 = n0 + 1 < a.N;
+  const int64_t c0 = valid0 ? n0 : a.N - 1, c1 = valid1 ? n0 + 1 : a.N - 1;  // clamped: loads stay in bounds
 
-  // ---- prologue: stage this tile's sim-independent tables; fold the next-grid interpolation into the coefficients
-  for (int i = threadIdx.x; i < gcount * D; i += blockDim.x) {
-    const int g = i / D, d = i - g * D;
-    DevDecision e = a.decisions[(size_t)(g0 + g) * D + d];
-    s.dec[i] = e;
-    double *c = s.coef + (size_t)i * KP;
-    if (!a.terminal_mode) {
-      const double *gl = a.gamma + (size_t)e.lower * K, *gu = a.gamma + (size_t)e.upper * K;
+  // per-path state: price, basis row of this period (continuation value) and of the previous one (regression sums)
+  double price0, price1;
+  if (a.spot) {
+    price0 = a.spot[c0];
+    price1 = a.spot[c1];
+  } else {
+    price0 = price1 = a.const_price;
+  }
+  double q0[KP], q1[KP], p0[KP], p1[KP];
 #pragma unroll
-      for (int k = 0; k < KP; ++k) c[k] = (k < K) ? (e.lower == e.upper ? gl[k] : gu[k] * e.upper_w + gl[k] * e.lower_w) : 0.0;
+  for (int k = 0; k < KP; ++k) {
+    q0[k] = q1[k] = p0[k] = p1[k] = 0.0;
+    if (k < K) {
+      if (a.q_this) {
+        q0[k] = a.q_this[(size_t)k * a.pitch + c0];
+        q1[k] = a.q_this[(size_t)k * a.pitch + c1];
+      }
+      if (a.q_prev) {
+        p0[k] = valid0 ? a.q_prev[(size_t)k * a.pitch + c0] : 0.0;
+        p1[k] = valid1 ? a.q_prev[(size_t)k * a.pitch + c1] : 0.0;
+      }
     }
   }
-  for (int i = threadIdx.x; i < gcount; i += blockDim.x) {
-    s.inv_cost[i] = a.inventory_cost ? a.inventory_cost[g0 + i] : 0.0;
-    s.nd[i] = a.num_decisions ? a.num_decisions[g0 + i] : 0;
+  if (!a.terminal_mode && !a.q_this) q0[0] = q1[0] = 1.0;  // mean mode: continuation value = gamma[g][0]
+  if (a.accumulate && !a.q_prev) {                          // next regression is the sample mean: sum of V
+    p0[0] = valid0 ? 1.0 : 0.0;
+    p1[0] = valid1 ? 1.0 : 0.0;
   }
-  for (int i = threadIdx.x; i < K * K; i += blockDim.x) {
-    if (a.basis_this.rinv) s.rinv_this[i] = dd{a.basis_this.rinv[2 * i], a.basis_this.rinv[2 * i + 1]};
-    if (a.accumulate && a.basis_prev.rinv) s.rinv_prev[i] = dd{a.basis_prev.rinv[2 * i], a.basis_prev.rinv[2 * i + 1]};
-  }
-  for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s.pw[i] = a.powers[i];
-  for (int i = threadIdx.x; i < kWarps * kMaxGridTile * acc_k; i += blockDim.x) s.acc[i] = 0.0;
-  __syncthreads();
-
   const double df = a.settle_df;
-  for (int tile = 0; tile < a.tiles_per_chunk; ++tile) {
-    const int64_t n0 = ((int64_t)chunk * a.tiles_per_chunk + tile) * kTilePaths + (int64_t)threadIdx.x * kPathsPerThread;
-    if (n0 - threadIdx.x * kPathsPerThread >= a.N) break;  // whole tile is past the end (uniform across the CTA)
-    bool valid[2] = {n0 < a.N, n0 + 1 < a.N};
-    int64_t nn[2] = {valid[0] ? n0 : a.N - 1, valid[1] ? n0 + 1 : a.N - 1};  // clamped: loads stay in bounds
+  const int sub_begin = blockIdx.x * a.subtiles_per_cta;
+  const int sub_end = min(sub_begin + a.subtiles_per_cta, (a.G + TG - 1) / TG);
 
-    double q[2][KP], qp[2][KP], price[2];
+  for (int sub = sub_begin; sub < sub_end; ++sub) {
+    const int g0 = sub * TG;
+    const int gcount = min(TG, a.G - g0);
+    __syncthreads();  // the previous sub-tile's tables and partial sums are no longer in use
+    // ---- stage this sub-tile's sim-independent tables; fold the next-grid interpolation into the coefficients
+    if (!a.terminal_mode) {
+      for (int i = threadIdx.x; i < gcount * D; i += blockDim.x) {
+        const int g = i / D;
+        const DevDecision e = a.decisions[(size_t)g0 * D + i];
+        s_dec[i] = e;
+        double *c = s_coef + (size_t)i * KP;
+        if (i - g * D < a.num_decisions[g0 + g]) {
+          const double *gl = a.gamma + (size_t)e.lower * K, *gu = a.gamma + (size_t)e.upper * K;
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      if (a.terminal_mode) {
-#pragma unroll
-        for (int k = 0; k < KP; ++k) q[j][k] = 0.0;
-        price[j] = a.spot[nn[j]];
-      } else {
-        eval_q<KP>(a.basis_this, s.pw, s.rinv_this, K, F, nn[j], valid[j], q[j]);
-        price[j] = a.spot ? a.spot[nn[j]] : a.const_price;
+          for (int k = 0; k < KP; ++k) c[k] = (k < K) ? (e.lower == e.upper ? gl[k] : gu[k] * e.upper_w + gl[k] * e.lower_w) : 0.0;
+        }
       }
-      if (a.accumulate) {
-        eval_q<KP>(a.basis_prev, s.pw, s.rinv_prev, K, F, nn[j], valid[j], qp[j]);
-      } else {
-#pragma unroll
-        for (int k = 0; k < KP; ++k) qp[j][k] = 0.0;
+      for (int i = threadIdx.x; i < gcount; i += blockDim.x) {
+        s_inv_cost[i] = a.inventory_cost[g0 + i];
+        s_nd[i] = a.num_decisions[g0 + i];
       }
     }
+    __syncthreads();
 
     for (int g = 0; g < gcount; ++g) {
-      double v[2];
+      double v0, v1;
       if (a.terminal_mode) {
         // V_T[g][n] = TerminalStorageNpv(S_T[n], grid_T[g]) (LSV.cs:121-131)
         const double inv = a.grid_this[g0 + g];
-#pragma unroll
-        for (int j = 0; j < 2; ++j)
-          v[j] = ((a.terminal[3] * (price[j] * inv) + a.terminal[1] * price[j]) + a.terminal[2] * inv) + a.terminal[0];
+        v0 = ((a.terminal[3] * (price0 * inv) + a.terminal[1] * price0) + a.terminal[2] * inv) + a.terminal[0];
+        v1 = ((a.terminal[3] * (price1 * inv) + a.terminal[1] * price1) + a.terminal[2] * inv) + a.terminal[0];
       } else {
-        const int nd = s.nd[g];
-        const double inv_cost = s.inv_cost[g];
-        const DevDecision *dec = s.dec + (size_t)g * D;
-        const double *coef = s.coef + (size_t)g * D * KP;
+        const int nd = s_nd[g];
+        const double inv_cost = s_inv_cost[g];
+        const DevDecision *dec = s_dec + (size_t)g * D;
+        const double *coef = s_coef + (size_t)g * D * KP;
+        double best0 = 0.0, best1 = 0.0, bc0 = 0.0, bc1 = 0.0;
+        int bd0 = 0, bd1 = 0;
+        for (int d = 0; d < nd; ++d) {
+          const double *c = coef + (size_t)d * KP;
+          const double neg_volume = -dec[d].volume, neg_consumed = -dec[d].consumed, cost = dec[d].cost_npv;
+          double cont0 = q0[0] * c[0], cont1 = q1[0] * c[0];
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          double best = 0.0, best_c = 0.0;
-          int best_d = 0;
-          for (int d = 0; d < nd; ++d) {
-            const DevDecision &e = dec[d];
-            const double *c = coef + (size_t)d * KP;
-            double cont = q[j][0] * c[0];
-#pragma unroll
-            for (int k = 1; k < KP; ++k) cont = __fma_rn(q[j][k], c[k], cont);
-            // LSV.cs:317-325, same association
-            const double inject_withdraw_npv = (-e.volume * price[j]) * df;
-            const double consumed_npv = (-e.consumed * price[j]) * df;
-            const double immediate = (inject_withdraw_npv - e.cost_npv) + consumed_npv;
-            const double total = (immediate + cont) - inv_cost;
-            if (d == 0 || total > best) {  // strict >: first maximum wins (SH.cs:206-221)
-              best = total;
-              best_c = cont;
-              best_d = d;
-            }
+          for (int k = 1; k < KP; ++k) {
+            cont0 = __fma_rn(q0[k], c[k], cont0);
+            cont1 = __fma_rn(q1[k], c[k], cont1);
           }
-          const DevDecision &e = dec[best_d];
-          const double lo = a.v_next[(size_t)e.lower * a.pitch + nn[j]];
-          double actual = lo;
-          if (e.upper != e.lower) {
-            const double up = a.v_next[(size_t)e.upper * a.pitch + nn[j]];
-            actual = up * e.upper_w + lo * e.lower_w;  // WeightedAverage (LSV.cs:828-836)
+          // LSV.cs:317-325, same association: ((-v*S)*DF - cost + (-consumed*S)*DF) + continuation - inventoryCost
+          const double t0 = ((((neg_volume * price0) * df - cost) + (neg_consumed * price0) * df) + cont0) - inv_cost;
+          const double t1 = ((((neg_volume * price1) * df - cost) + (neg_consumed * price1) * df) + cont1) - inv_cost;
+          if (d == 0 || t0 > best0) {  // strict >: first maximum wins (SH.cs:206-221)
+            best0 = t0;
+            bc0 = cont0;
+            bd0 = d;
           }
-          v[j] = best + (-best_c + actual);  // LSV.cs:330-335
+          if (d == 0 || t1 > best1) {
+            best1 = t1;
+            bc1 = cont1;
+            bd1 = d;
+          }
         }
+        // realised continuation value of the chosen decision: WeightedAverage of v_next rows (LSV.cs:296-302, 828-836)
+        const DevDecision &e0 = dec[bd0], &e1 = dec[bd1];
+        const double lo0 = a.v_next[(size_t)e0.lower * a.pitch + c0];
+        const double lo1 = a.v_next[(size_t)e1.lower * a.pitch + c1];
+        double act0 = lo0, act1 = lo1;
+        if (e0.upper != e0.lower) act0 = a.v_next[(size_t)e0.upper * a.pitch + c0] * e0.upper_w + lo0 * e0.lower_w;
+        if (e1.upper != e1.lower) act1 = a.v_next[(size_t)e1.upper * a.pitch + c1] * e1.upper_w + lo1 * e1.lower_w;
+        v0 = best0 + (-bc0 + act0);  // LSV.cs:330-335
+        v1 = best1 + (-bc1 + act1);
       }
-      if (!valid[0]) v[0] = 0.0;
-      if (!valid[1]) v[1] = 0.0;
-      if (valid[0]) *reinterpret_cast<double2 *>(a.v_this + (size_t)(g0 + g) * a.pitch + n0) = make_double2(v[0], v[1]);
+      if (valid0) *reinterpret_cast<double2 *>(a.v_this + (size_t)(g0 + g) * a.pitch + n0) = make_double2(v0, valid1 ? v1 : 0.0);
 
       if (a.accumulate) {
         // q_prev^T V for the regression of the next backward step, reduced over the warp in a fixed order
@@ -377,28 +403,21 @@ __global__ void __launch_bounds__(kThreads) backward_step_kernel(BackwardStepArg
         for (int half = 0; half < ACC; half += 8) {
           double part[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            part[k] = 0.0;
-          }
-#pragma unroll
-          for (int k = 0; k < KP; ++k) {
-            if (k >= half && k < half + 8) part[k - half] = __fma_rn(qp[1][k], v[1], qp[0][k] * v[0]);
-          }
+          for (int k = 0; k < 8; ++k) part[k] = (half + k < KP) ? __fma_rn(p1[(half + k < KP) ? half + k : 0], v1, p0[(half + k < KP) ? half + k : 0] * v0) : 0.0;
           int kidx;
-          double total = warp_reduce8(part, lane, kidx);
-          if ((lane & 3) == 0) s.acc[((size_t)warp * kMaxGridTile + g) * acc_k + half + kidx] += total;
+          const double total = warp_reduce8(part, lane, kidx);
+          if ((lane & 3) == 0) s_acc[((size_t)warp * TG + g) * ACC + half + kidx] = total;
         }
       }
     }
-  }
 
-  if (a.accumulate) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < gcount * acc_k; i += blockDim.x) {
-      const int g = i / acc_k, k = i - g * acc_k;
-      double sum = s.acc[((size_t)0 * kMaxGridTile + g) * acc_k + k];
-      for (int w = 1; w < kWarps; ++w) sum += s.acc[((size_t)w * kMaxGridTile + g) * acc_k + k];
-      a.partials[((size_t)chunk * a.G + g0 + g) * acc_k + k] = sum;
+    if (a.accumulate) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < gcount * ACC; i += blockDim.x) {
+        double sum = s_acc[i];
+        for (int w = 1; w < kWarps; ++w) sum += s_acc[(size_t)w * TG * ACC + i];
+        a.partials[((size_t)tile * a.G + g0) * ACC + i] = sum;
+      }
     }
   }
 }
@@ -760,6 +779,9 @@ void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t sme
       if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       backward_step_kernel<KP><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
       break;
+    case 4:
+      basis_kernel<KP><<<grid, block, 0, stream>>>(*static_cast<const BasisArgs *>(args));
+      break;
     case 3:
       if (smem > 48 * 1024) cudaFuncSetAttribute(forward_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       forward_kernel<KP><<<grid, block, smem, stream>>>(*static_cast<const ForwardArgs *>(args));
@@ -786,11 +808,10 @@ void dispatch(int KP, int which, const void *args, dim3 grid, dim3 block, size_t
 
 int padded_basis(int K) { return K <= 8 ? K : (K <= 12 ? 12 : 16); }
 
-size_t backward_smem_bytes(int KP, int D, int K, int F, int acc_k) {
-  auto up = [](size_t b) { return (b + 15) & ~size_t(15); };
-  return up(sizeof(DevDecision) * kMaxGridTile * D) + up(sizeof(double) * kMaxGridTile * D * KP) + up(sizeof(double) * kMaxGridTile) +
-         up(sizeof(int32_t) * kMaxGridTile) + 2 * up(sizeof(dd) * K * K) + up(sizeof(int32_t) * K * (1 + F)) +
-         up(sizeof(double) * kWarps * kMaxGridTile * acc_k);
+size_t backward_smem_bytes(int KP, int D) {
+  const int acc = KP <= 8 ? 8 : 16;
+  return sizeof(DevDecision) * kMaxGridTile * D + sizeof(double) * ((size_t)kMaxGridTile * D * KP + kMaxGridTile) +
+         sizeof(double) * kWarps * kMaxGridTile * acc + sizeof(int32_t) * kMaxGridTile + 16;
 }
 
 size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width) {
@@ -804,10 +825,12 @@ void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t 
 void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream) {
   dispatch(padded_basis(a.K), 1, &a, dim3(num_slots), dim3(64), 0, stream);
 }
-void launch_backward_step(const BackwardStepArgs &a, int num_chunks, cudaStream_t stream) {
+void launch_backward_step(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream) {
   const int KP = padded_basis(a.K);
-  const int gtiles = (a.G + kMaxGridTile - 1) / kMaxGridTile;
-  dispatch(KP, 2, &a, dim3(gtiles, num_chunks), dim3(kThreads), backward_smem_bytes(KP, a.D, a.K, a.F, a.acc_k), stream);
+  dispatch(KP, 2, &a, dim3(gsplit, (unsigned)num_tiles), dim3(kThreads), backward_smem_bytes(KP, a.D), stream);
+}
+void launch_basis(const BasisArgs &a, cudaStream_t stream) {
+  dispatch(padded_basis(a.K), 4, &a, dim3((unsigned)((a.N + 255) / 256)), dim3(256), 0, stream);
 }
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream) {
   const int threads = 256 / a.acc_k * a.acc_k;

@@ -26,6 +26,14 @@ struct CholeskyArgs {
   int32_t *error_flag;
 };
 
+struct BasisArgs {
+  int64_t N, pitch;
+  int K, F;
+  BasisSpec spec;          // regression simulations of the period + its R^-1
+  const int32_t *powers;
+  double *q_out;           // [K][pitch]
+};
+
 struct ReduceArgs {
   const double *partials;  // [num_chunks][G][acc_k]
   int num_chunks, G, K, acc_k;
@@ -36,12 +44,13 @@ struct ReduceArgs {
 
 int padded_basis(int K);
 inline int acc_width(int K) { return padded_basis(K) <= 8 ? 8 : 16; }
-size_t backward_smem_bytes(int KP, int D, int K, int F, int acc_k);
+size_t backward_smem_bytes(int KP, int D);
 size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width);
 
 void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream);
 void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream);
-void launch_backward_step(const BackwardStepArgs &a, int num_chunks, cudaStream_t stream);
+void launch_backward_step(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
+void launch_basis(const BasisArgs &a, cudaStream_t stream);
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream);
 // out[i] = sum over ranks r of all[r][i] (rank order); mean_mode: component 0 of every K-vector divided by total_paths, rest 0

@@ -93,7 +93,7 @@ struct lsmc_handle {
   cudaStream_t stream = nullptr;
   SimSet sims[2];
   DeviceBuffer<double> v_a, v_b, grids, gamma, rinv, partials, gram_partials, inv_cost, pv, final_inv, step_sums, step_totals,
-      block_sums, gather_buf, ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
+      block_sums, gather_buf, qbuf[2], ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
   DeviceBuffer<DevDecision> decisions;
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
   DeviceBuffer<DevPeriodParams> period_params;
@@ -431,20 +431,32 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   const int64_t num_tiles = (N + kTilePaths - 1) / kTilePaths;
   int sm_count = 148;
   cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device);
+  auto q_buffer = [&](int period) { return h->qbuf[period & 1].ptr; };
+  auto has_basis = [&](int period) { return period >= first_reg && period < P; };
+  auto launch_basis_for = [&](int period) {
+    // orthonormal basis rows of the regression simulations of `period` (LSV.cs:191 PopulateDesignMatrix + :193-196 QR)
+    BasisArgs b{};
+    b.N = N;
+    b.pitch = h->pitch;
+    b.K = K;
+    b.F = F;
+    b.spec = basis_spec(*h, 0, period);
+    b.powers = h->d_powers.ptr;
+    b.q_out = q_buffer(period);
+    launch_basis(b, st);
+    launches++;
+  };
   auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this) {
     const PeriodTables &pt = h->tables.periods[p];
+    if (has_basis(p - 1)) launch_basis_for(p - 1);
     BackwardStepArgs a{};
     a.N = N;
     a.pitch = h->pitch;
     a.G = (int)pt.grid.size();
-    a.Gn = terminal ? 0 : (int)h->tables.periods[p + 1].grid.size();
-    a.D = terminal ? 0 : D;
+    a.D = terminal ? 1 : D;
     a.K = K;
-    a.F = F;
     a.v_next = v_next;
     a.v_this = v_this;
-    a.powers = h->d_powers.ptr;
-    a.acc_k = h->acc_k;
     a.terminal_mode = terminal ? 1 : 0;
     if (terminal) {
       a.grid_this = h->grids.ptr + (size_t)p * Gmax;
@@ -456,28 +468,29 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       a.num_decisions = h->num_decisions.ptr + h->table_offset[p];
       a.inventory_cost = h->inv_cost.ptr + h->table_offset[p];
       a.settle_df = h->settle_df[p];
-      a.basis_this = basis_spec(*h, 0, p);
-      if (a.basis_this.mean_mode) {
+      if (has_basis(p)) {
+        a.q_this = q_buffer(p);
+        a.spot = h->sims[0].spot + (size_t)(p - h->first_sim) * N;
+      } else {  // current period: deterministic price, sample-mean continuation value (LSV.cs:174-185,232-236)
+        a.q_this = nullptr;
         a.spot = nullptr;
         a.const_price = h->forward_price[p];
-      } else {
-        a.spot = a.basis_this.spot;
       }
     }
     a.accumulate = p > 0 ? 1 : 0;
-    if (a.accumulate) a.basis_prev = basis_spec(*h, 0, p - 1);
+    a.q_prev = has_basis(p - 1) ? q_buffer(p - 1) : nullptr;
     a.partials = h->partials.ptr;
-    // enough CTAs for several waves, but long enough chunks that the partial-sum traffic stays small
-    const int gtiles = (a.G + kMaxGridTile - 1) / kMaxGridTile;
-    int64_t want_chunks = std::max<int64_t>(1, (int64_t)sm_count * 24 / gtiles);
-    int tiles_per_chunk = (int)std::max<int64_t>(1, std::min<int64_t>(16, num_tiles / want_chunks));
-    const int num_chunks = (int)((num_tiles + tiles_per_chunk - 1) / tiles_per_chunk);
-    a.tiles_per_chunk = tiles_per_chunk;
+    // split the inventory grid over several CTAs only when there are too few path tiles to fill the GPU
+    const int subtiles = (a.G + kMaxGridTile - 1) / kMaxGridTile;
+    const int64_t slots = (int64_t)sm_count * 5;
+    int gsplit = (int)std::min<int64_t>(subtiles, std::max<int64_t>(1, (4 * slots + num_tiles - 1) / num_tiles));
+    a.subtiles_per_cta = (subtiles + gsplit - 1) / gsplit;
+    gsplit = (subtiles + a.subtiles_per_cta - 1) / a.subtiles_per_cta;
     if (!terminal) cudaEventRecord(step_events[2 * p], st);
-    launch_backward_step(a, num_chunks, st);
+    launch_backward_step(a, gsplit, num_tiles, st);
     if (!terminal) cudaEventRecord(step_events[2 * p + 1], st);
     launches++;
-    return num_chunks;
+    return (int)num_tiles;
   };
   auto reduce_gamma = [&](int p, int G_next, int num_chunks) {
     // regression coefficients of V_{p+1} on period p's basis (LSV.cs:199-212) from the partial sums the kernel that
@@ -721,6 +734,8 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     CUDA_OK(cudaMemset(h->rinv.ptr, 0, h->rinv.count * sizeof(double)));
     const int64_t num_tiles = (h->N + kTilePaths - 1) / kTilePaths;
     h->partials.allocate((size_t)num_tiles * h->Gmax * h->acc_k);
+    h->qbuf[0].allocate((size_t)h->K * h->pitch);
+    h->qbuf[1].allocate((size_t)h->K * h->pitch);
     h->pv.allocate(h->N);
     h->final_inv.allocate(h->N);
     h->error_flag.allocate(1);
