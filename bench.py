@@ -259,6 +259,8 @@ def run_gpu(args):
         r = one_run(h)
         barrier()
         times.append(time.perf_counter() - t0)
+        phases = {"gram_cholesky_ms": r.ms_pseudo_inverse, "backward_ms": r.ms_backward, "forward_ms": r.ms_forward,
+                  "run_total_ms": r.ms_total}
         kernel_ms += r.ms_backward_kernel
         bk_launches += r.backward_kernel_launches
         launches += r.kernel_launches
@@ -311,7 +313,7 @@ def run_gpu(args):
            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
            "config": workload_config(args, n, world),
            "evals_per_step": evals_total, "mean_grid_points": mean_grid, "npv": npv,
-           "device_ms_per_step": device_ms / args.steps, "setup_seconds_untimed": setup_s,
+           "device_ms_per_step": device_ms / args.steps, "phases_last_step": phases, "setup_seconds_untimed": setup_s,
            "roofline": {"bound": "hbm", "kernel": "backward_step_kernel<7>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                         "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
                         "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": 1000.0 * avg_kernel_s,

@@ -11,7 +11,7 @@ constexpr int kPathsPerThread = 2;       // double2 vectorisation over adjacent 
 constexpr int kTilePaths = kThreads * kPathsPerThread;
 constexpr int kWarps = kThreads / 32;
 constexpr int kAccK = 8;                 // regression partial sums are stored padded to 8 (or 16) per grid point
-constexpr int kMaxGridTile = 32;         // inventory-grid points per CTA in the backward kernel
+constexpr int kMaxGridTile = 16;         // inventory-grid points per CTA in the backward kernel
 
 // Device copy of host_model.hpp's DecisionEntry (same layout).
 struct DevDecision {

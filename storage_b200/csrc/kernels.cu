@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "dd.cuh"
 #include "device_types.hpp"
@@ -273,52 +274,91 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
 // One CTA = one tile of 256 paths (128 threads x double2) x a contiguous range of inventory-grid sub-tiles.  Within the
 // CTA the grid points are swept in ascending order, so the rows of v_next a decision interpolates between are re-used
 // from L1 by the neighbouring grid points and each row comes from HBM once.
+//
+// The regression sums of the next backward step, sum_n q_prev[n][k] * V[g][n], are a dense skinny FP64 GEMM
+// (K x paths) x (paths x grid points).  Each warp runs it on the tensor cores (mma.sync m8n8k4 f64) over its own 64
+// paths from a warp-private shared-memory tile, 8 grid points at a time; warps are combined in a fixed order.
+struct __align__(16) DecisionA {  // one LDS.128 each
+  double neg_volume, neg_consumed, cost_npv, lower_w;
+};
+struct __align__(16) DecisionB {
+  double upper_w;
+  long long lower_off, upper_off;  // row offsets into v_next, in doubles
+  double pad;
+};
+
+constexpr int kWarpPaths = 32 * kPathsPerThread;  // 64 paths per warp
+constexpr int kTilePitch = kWarpPaths + 4;        // row pitch of the warp-private tiles: conflict-free fragment loads
+
+__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
 template <int KP>
 __global__ void __launch_bounds__(kThreads) backward_step_kernel(BackwardStepArgs a) {
-  constexpr int ACC = KP <= 8 ? 8 : 16;  // width of a stored partial-sum row
+  constexpr int ACC = KP <= 8 ? 8 : 16;       // width of a stored partial-sum row
+  constexpr int KC = (KP + 1) & ~1;           // coefficient row padded to an even length (16-byte rows)
   constexpr int TG = kMaxGridTile;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int K = a.K, D = a.D;
-  // dynamic smem: dec [TG][D] | coef [TG][D][KP] | inv_cost [TG] | nd [TG] | acc [kWarps][TG][ACC]
-  DevDecision *s_dec = reinterpret_cast<DevDecision *>(smem_raw);
-  double *s_coef = reinterpret_cast<double *>(s_dec + (size_t)TG * D);
-  double *s_inv_cost = s_coef + (size_t)TG * D * KP;
-  double *s_acc = s_inv_cost + TG;
-  int32_t *s_nd = reinterpret_cast<int32_t *>(s_acc + (size_t)kWarps * TG * ACC);
+  // dynamic smem: decA [TG][D] | decB [TG][D] | coef [TG][D][KC] | vtile [kWarps][8][pitch] | qtile [kWarps][ACC][pitch]
+  //               | acc [kWarps][ACC][TG] | inv_cost [TG] | nd [TG]
+  DecisionA *s_a = reinterpret_cast<DecisionA *>(smem_raw);
+  DecisionB *s_b = reinterpret_cast<DecisionB *>(s_a + (size_t)TG * D);
+  double *s_coef = reinterpret_cast<double *>(s_b + (size_t)TG * D);
+  double *s_vtile = s_coef + (size_t)TG * D * KC;
+  double *s_qtile = s_vtile + (size_t)kWarps * 8 * kTilePitch;
+  double *s_acc = s_qtile + (size_t)kWarps * ACC * kTilePitch;
+  double *s_inv_cost = s_acc + (size_t)kWarps * ACC * TG;
+  int32_t *s_nd = reinterpret_cast<int32_t *>(s_inv_cost + TG);
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t tile = blockIdx.y;
   const int64_t n0 = tile * kTilePaths + (int64_t)threadIdx.x * kPathsPerThread;
   const bool valid0 = n0 < a.N, valid1 = n0 + 1 < a.N;
-  const int64_t c0 = valid0 ? n0 : a.N - 1, c1 = valid1 ? n0 + 1 : a.N - 1;  // clamped: loads stay in bounds
+  const int64_t c0 = valid0 ? n0 : ((a.N - 1) & ~int64_t(1));  // clamped, even: vector loads stay inside the padded row
+  const int64_t c1 = valid1 ? n0 + 1 : a.N - 1;
 
-  // per-path state: price, basis row of this period (continuation value) and of the previous one (regression sums)
   double price0, price1;
   if (a.spot) {
-    price0 = a.spot[c0];
+    price0 = a.spot[valid0 ? n0 : a.N - 1];
     price1 = a.spot[c1];
   } else {
     price0 = price1 = a.const_price;
   }
-  double q0[KP], q1[KP], p0[KP], p1[KP];
+  // basis row of this period (continuation value)
+  double q0[KP], q1[KP];
 #pragma unroll
   for (int k = 0; k < KP; ++k) {
-    q0[k] = q1[k] = p0[k] = p1[k] = 0.0;
-    if (k < K) {
-      if (a.q_this) {
-        q0[k] = a.q_this[(size_t)k * a.pitch + c0];
-        q1[k] = a.q_this[(size_t)k * a.pitch + c1];
-      }
-      if (a.q_prev) {
-        p0[k] = valid0 ? a.q_prev[(size_t)k * a.pitch + c0] : 0.0;
-        p1[k] = valid1 ? a.q_prev[(size_t)k * a.pitch + c1] : 0.0;
-      }
+    q0[k] = q1[k] = 0.0;
+    if (k < K && a.q_this) {
+      const double2 t = *reinterpret_cast<const double2 *>(a.q_this + (size_t)k * a.pitch + c0);
+      q0[k] = t.x;
+      q1[k] = t.y;
     }
   }
   if (!a.terminal_mode && !a.q_this) q0[0] = q1[0] = 1.0;  // mean mode: continuation value = gamma[g][0]
-  if (a.accumulate && !a.q_prev) {                          // next regression is the sample mean: sum of V
-    p0[0] = valid0 ? 1.0 : 0.0;
-    p1[0] = valid1 ? 1.0 : 0.0;
+
+  // basis rows of the previous period for the regression sums, staged as the A operand of the warp's GEMM
+  double *my_q = s_qtile + (size_t)warp * ACC * kTilePitch;
+  double *my_v = s_vtile + (size_t)warp * 8 * kTilePitch;
+  if (a.accumulate) {
+#pragma unroll
+    for (int k = 0; k < ACC; ++k) {
+      double2 t = make_double2(0.0, 0.0);
+      if (k < K) {
+        if (a.q_prev) {
+          t = *reinterpret_cast<const double2 *>(a.q_prev + (size_t)k * a.pitch + c0);
+        } else if (k == 0) {
+          t = make_double2(1.0, 1.0);  // next regression is the sample mean: plain sum of V
+        }
+      }
+      if (!valid0) t.x = 0.0;
+      if (!valid1) t.y = 0.0;
+      *reinterpret_cast<double2 *>(my_q + (size_t)k * kTilePitch + 2 * lane) = t;
+    }
   }
   const double df = a.settle_df;
   const int sub_begin = blockIdx.x * a.subtiles_per_cta;
@@ -332,13 +372,14 @@ __global__ void __launch_bounds__(kThreads) backward_step_kernel(BackwardStepArg
     if (!a.terminal_mode) {
       for (int i = threadIdx.x; i < gcount * D; i += blockDim.x) {
         const int g = i / D;
-        const DevDecision e = a.decisions[(size_t)g0 * D + i];
-        s_dec[i] = e;
-        double *c = s_coef + (size_t)i * KP;
         if (i - g * D < a.num_decisions[g0 + g]) {
+          const DevDecision e = a.decisions[(size_t)g0 * D + i];
+          s_a[i] = DecisionA{-e.volume, -e.consumed, e.cost_npv, e.lower_w};
+          s_b[i] = DecisionB{e.upper_w, (long long)e.lower * a.pitch, (long long)e.upper * a.pitch, 0.0};
+          double *c = s_coef + (size_t)i * KC;
           const double *gl = a.gamma + (size_t)e.lower * K, *gu = a.gamma + (size_t)e.upper * K;
 #pragma unroll
-          for (int k = 0; k < KP; ++k) c[k] = (k < K) ? (e.lower == e.upper ? gl[k] : gu[k] * e.upper_w + gl[k] * e.lower_w) : 0.0;
+          for (int k = 0; k < KC; ++k) c[k] = (k < K) ? (e.lower == e.upper ? gl[k] : gu[k] * e.upper_w + gl[k] * e.lower_w) : 0.0;
         }
       }
       for (int i = threadIdx.x; i < gcount; i += blockDim.x) {
@@ -348,75 +389,128 @@ __global__ void __launch_bounds__(kThreads) backward_step_kernel(BackwardStepArg
     }
     __syncthreads();
 
-    for (int g = 0; g < gcount; ++g) {
-      double v0, v1;
-      if (a.terminal_mode) {
-        // V_T[g][n] = TerminalStorageNpv(S_T[n], grid_T[g]) (LSV.cs:121-131)
-        const double inv = a.grid_this[g0 + g];
-        v0 = ((a.terminal[3] * (price0 * inv) + a.terminal[1] * price0) + a.terminal[2] * inv) + a.terminal[0];
-        v1 = ((a.terminal[3] * (price1 * inv) + a.terminal[1] * price1) + a.terminal[2] * inv) + a.terminal[0];
-      } else {
-        const int nd = s_nd[g];
-        const double inv_cost = s_inv_cost[g];
-        const DevDecision *dec = s_dec + (size_t)g * D;
-        const double *coef = s_coef + (size_t)g * D * KP;
-        double best0 = 0.0, best1 = 0.0, bc0 = 0.0, bc1 = 0.0;
-        int bd0 = 0, bd1 = 0;
-        for (int d = 0; d < nd; ++d) {
-          const double *c = coef + (size_t)d * KP;
-          const double neg_volume = -dec[d].volume, neg_consumed = -dec[d].consumed, cost = dec[d].cost_npv;
-          double cont0 = q0[0] * c[0], cont1 = q1[0] * c[0];
+    double2 pre_lo[3], pre_up[3];  // v_next rows of the next grid point to evaluate (software prefetch, D <= 3 only)
 #pragma unroll
-          for (int k = 1; k < KP; ++k) {
-            cont0 = __fma_rn(q0[k], c[k], cont0);
-            cont1 = __fma_rn(q1[k], c[k], cont1);
-          }
-          // LSV.cs:317-325, same association: ((-v*S)*DF - cost + (-consumed*S)*DF) + continuation - inventoryCost
-          const double t0 = ((((neg_volume * price0) * df - cost) + (neg_consumed * price0) * df) + cont0) - inv_cost;
-          const double t1 = ((((neg_volume * price1) * df - cost) + (neg_consumed * price1) * df) + cont1) - inv_cost;
-          if (d == 0 || t0 > best0) {  // strict >: first maximum wins (SH.cs:206-221)
-            best0 = t0;
-            bc0 = cont0;
-            bd0 = d;
-          }
-          if (d == 0 || t1 > best1) {
-            best1 = t1;
-            bc1 = cont1;
-            bd1 = d;
-          }
+    for (int d = 0; d < 3; ++d) pre_lo[d] = pre_up[d] = make_double2(0.0, 0.0);
+    if (!a.terminal_mode && D <= 3) {
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        if (d < s_nd[0]) {
+          const DecisionB nb = s_b[d];
+          pre_lo[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.lower_off + c0);
+          pre_up[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.upper_off + c0);
         }
-        // realised continuation value of the chosen decision: WeightedAverage of v_next rows (LSV.cs:296-302, 828-836)
-        const DevDecision &e0 = dec[bd0], &e1 = dec[bd1];
-        const double lo0 = a.v_next[(size_t)e0.lower * a.pitch + c0];
-        const double lo1 = a.v_next[(size_t)e1.lower * a.pitch + c1];
-        double act0 = lo0, act1 = lo1;
-        if (e0.upper != e0.lower) act0 = a.v_next[(size_t)e0.upper * a.pitch + c0] * e0.upper_w + lo0 * e0.lower_w;
-        if (e1.upper != e1.lower) act1 = a.v_next[(size_t)e1.upper * a.pitch + c1] * e1.upper_w + lo1 * e1.lower_w;
-        v0 = best0 + (-bc0 + act0);  // LSV.cs:330-335
-        v1 = best1 + (-bc1 + act1);
       }
-      if (valid0) *reinterpret_cast<double2 *>(a.v_this + (size_t)(g0 + g) * a.pitch + n0) = make_double2(v0, valid1 ? v1 : 0.0);
+    }
+
+    for (int gg = 0; gg < gcount; gg += 8) {
+      const int gn = min(8, gcount - gg);
+      for (int gi = 0; gi < 8; ++gi) {
+        double v0 = 0.0, v1 = 0.0;
+        if (gi < gn) {
+          const int g = gg + gi;
+          if (a.terminal_mode) {
+            // V_T[g][n] = TerminalStorageNpv(S_T[n], grid_T[g]) (LSV.cs:121-131)
+            const double inv = a.grid_this[g0 + g];
+            v0 = ((a.terminal[3] * (price0 * inv) + a.terminal[1] * price0) + a.terminal[2] * inv) + a.terminal[0];
+            v1 = ((a.terminal[3] * (price1 * inv) + a.terminal[1] * price1) + a.terminal[2] * inv) + a.terminal[0];
+          } else {
+            const int nd = s_nd[g];
+            const double inv_cost = s_inv_cost[g];
+            double best0 = 0.0, best1 = 0.0, adj0 = 0.0, adj1 = 0.0;
+            auto evaluate = [&](int d, const double2 lo, const double2 up) {
+              const DecisionA da = s_a[g * D + d];
+              const double upper_w = s_b[g * D + d].upper_w;
+              const double *c = s_coef + (size_t)(g * D + d) * KC;
+              double cont0 = q0[0] * c[0], cont1 = q1[0] * c[0];
+#pragma unroll
+              for (int k = 1; k < KP; ++k) {
+                cont0 = __fma_rn(q0[k], c[k], cont0);
+                cont1 = __fma_rn(q1[k], c[k], cont1);
+              }
+              // LSV.cs:317-325, same association: ((-v*S)*DF - cost + (-consumed*S)*DF) + continuation - inventoryCost
+              const double t0 = ((((da.neg_volume * price0) * df - da.cost_npv) + (da.neg_consumed * price0) * df) + cont0) - inv_cost;
+              const double t1 = ((((da.neg_volume * price1) * df - da.cost_npv) + (da.neg_consumed * price1) * df) + cont1) - inv_cost;
+              // realised continuation value: WeightedAverage of the v_next rows (LSV.cs:296-302, 828-836); an exact grid
+              // hit has weights (1, 0) and reproduces the row bit for bit.  adj = -regressed + realised (LSV.cs:330-332)
+              const double a0 = -cont0 + (up.x * upper_w + lo.x * da.lower_w);
+              const double a1 = -cont1 + (up.y * upper_w + lo.y * da.lower_w);
+              if (d == 0 || t0 > best0) {  // strict >: first maximum wins (SH.cs:206-221)
+                best0 = t0;
+                adj0 = a0;
+              }
+              if (d == 0 || t1 > best1) {
+                best1 = t1;
+                adj1 = a1;
+              }
+            };
+            if (D <= 3) {
+              // common case (no extra decisions): the rows of v_next for this grid point were requested one grid point
+              // ago (pre_lo/pre_up); request the next grid point's rows before the arithmetic of this one
+              double2 cur_lo[3], cur_up[3];
+#pragma unroll
+              for (int d = 0; d < 3; ++d) {
+                cur_lo[d] = pre_lo[d];
+                cur_up[d] = pre_up[d];
+              }
+              const int gnext = g + 1;
+              if (gnext < gcount) {
+#pragma unroll
+                for (int d = 0; d < 3; ++d) {
+                  if (d < s_nd[gnext]) {
+                    const DecisionB nb = s_b[gnext * D + d];
+                    pre_lo[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.lower_off + c0);
+                    pre_up[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.upper_off + c0);
+                  }
+                }
+              }
+#pragma unroll
+              for (int d = 0; d < 3; ++d)
+                if (d < nd) evaluate(d, cur_lo[d], cur_up[d]);
+            } else {
+              for (int d = 0; d < nd; ++d) {
+                const DecisionB db = s_b[g * D + d];
+                evaluate(d, *reinterpret_cast<const double2 *>(a.v_next + db.lower_off + c0),
+                         *reinterpret_cast<const double2 *>(a.v_next + db.upper_off + c0));
+              }
+            }
+            v0 = best0 + adj0;  // LSV.cs:333
+            v1 = best1 + adj1;
+          }
+          if (!valid0) v0 = 0.0;
+          if (!valid1) v1 = 0.0;
+          if (valid0) *reinterpret_cast<double2 *>(a.v_this + (size_t)(g0 + g) * a.pitch + n0) = make_double2(v0, v1);
+        }
+        if (a.accumulate) *reinterpret_cast<double2 *>(my_v + (size_t)gi * kTilePitch + 2 * lane) = make_double2(v0, v1);
+      }
 
       if (a.accumulate) {
-        // q_prev^T V for the regression of the next backward step, reduced over the warp in a fixed order
+        // C[k][g] += sum over the warp's 64 paths of Q_prev[k][n] * V[g][n]: 16 k-steps of m8n8k4 per 8 basis rows
+        __syncwarp();
+        const int row = lane >> 2, col = lane & 3;
 #pragma unroll
-        for (int half = 0; half < ACC; half += 8) {
-          double part[8];
-#pragma unroll
-          for (int k = 0; k < 8; ++k) part[k] = (half + k < KP) ? __fma_rn(p1[(half + k < KP) ? half + k : 0], v1, p0[(half + k < KP) ? half + k : 0] * v0) : 0.0;
-          int kidx;
-          const double total = warp_reduce8(part, lane, kidx);
-          if ((lane & 3) == 0) s_acc[((size_t)warp * TG + g) * ACC + half + kidx] = total;
+        for (int mb = 0; mb < ACC; mb += 8) {
+          double acc0 = 0.0, acc1 = 0.0;
+          const double *qa = my_q + (size_t)(mb + row) * kTilePitch + col;
+          const double *vb = my_v + (size_t)row * kTilePitch + col;
+#pragma unroll 4
+          for (int p = 0; p < kWarpPaths; p += 4) dmma_m8n8k4(acc0, acc1, qa[p], vb[p]);
+          // C fragment: row = basis index mb + lane/4, columns = grid points 2*(lane%4) + {0,1} of this group
+          double *dst = s_acc + ((size_t)warp * ACC + mb + row) * TG + gg + 2 * col;
+          dst[0] = acc0;
+          dst[1] = acc1;
         }
+        __syncwarp();
       }
     }
 
     if (a.accumulate) {
       __syncthreads();
       for (int i = threadIdx.x; i < gcount * ACC; i += blockDim.x) {
-        double sum = s_acc[i];
-        for (int w = 1; w < kWarps; ++w) sum += s_acc[(size_t)w * TG * ACC + i];
-        a.partials[((size_t)tile * a.G + g0) * ACC + i] = sum;
+        const int g = i / ACC, k = i - g * ACC;
+        double sum = s_acc[((size_t)0 * ACC + k) * TG + g];
+        for (int w = 1; w < kWarps; ++w) sum += s_acc[((size_t)w * ACC + k) * TG + g];
+        a.partials[((size_t)tile * a.G + g0 + g) * ACC + k] = sum;
       }
     }
   }
@@ -777,6 +871,11 @@ void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t sme
       break;
     case 2:
       if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      {
+        static int carve = -2;
+        if (carve == -2) { const char *e = getenv("LSMC_CARVEOUT"); carve = e ? atoi(e) : -1; }
+        if (carve >= 0) cudaFuncSetAttribute(backward_step_kernel<KP>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+      }
       backward_step_kernel<KP><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
       break;
     case 4:
@@ -809,9 +908,9 @@ void dispatch(int KP, int which, const void *args, dim3 grid, dim3 block, size_t
 int padded_basis(int K) { return K <= 8 ? K : (K <= 12 ? 12 : 16); }
 
 size_t backward_smem_bytes(int KP, int D) {
-  const int acc = KP <= 8 ? 8 : 16;
-  return sizeof(DevDecision) * kMaxGridTile * D + sizeof(double) * ((size_t)kMaxGridTile * D * KP + kMaxGridTile) +
-         sizeof(double) * kWarps * kMaxGridTile * acc + sizeof(int32_t) * kMaxGridTile + 16;
+  const int acc = KP <= 8 ? 8 : 16, kc = (KP + 1) & ~1, tg = kMaxGridTile, pitch = 32 * kPathsPerThread + 4;
+  return (size_t)tg * D * 64 + sizeof(double) * ((size_t)tg * D * kc + (size_t)kWarps * 8 * pitch + (size_t)kWarps * acc * pitch +
+                                                (size_t)kWarps * acc * tg + tg) + sizeof(int32_t) * tg + 16;
 }
 
 size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width) {
