@@ -129,7 +129,7 @@ class lsmc_results(C.Structure):
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_double, C.c_void_p)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "liblsmc_b200.so")
+LIB_PATH = os.environ.get("LSMC_LIBRARY") or os.path.join(_HERE, "lib", "liblsmc_b200.so")  # override: tuning builds only
 
 # every symbol include/lsmc_b200.h declares: (name, restype, argtypes)
 _H = C.c_void_p

@@ -1,0 +1,73 @@
+// backward_common.cuh — pieces shared by the two variants of the backward-induction kernel (kernels.cu: rows of
+// v_next read through L1/L2; backward_ring.cu: rows staged once in a shared-memory ring by bulk TMA copies).
+#pragma once
+#include <cstdint>
+
+#include "device_types.hpp"
+
+namespace lsmc {
+
+struct __align__(16) DecisionA {  // one LDS.128 each
+  double neg_volume, neg_consumed, cost_npv, lower_w;
+};
+struct __align__(16) DecisionB {
+  double upper_w;
+  long long lower_off, upper_off;  // row offsets into v_next, in doubles
+  double pad;
+};
+struct __align__(16) DecisionR {  // ring variant: byte offsets of the two rows inside the shared-memory ring
+  double upper_w;
+  uint32_t lower_off, upper_off;
+};
+
+constexpr int kWarpPaths = 32 * kPathsPerThread;  // 64 paths per warp
+constexpr int kTilePitch = kWarpPaths + 4;        // row pitch of the warp-private tiles: conflict-free fragment loads
+
+__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+
+// Sim-independent coefficients of one decision: the next-grid interpolation folded into the regression coefficients
+// (continuation value = q . c), written as a KC-long row.
+template <int KC>
+__device__ __forceinline__ void fold_coefficients(const DevDecision &e, const double *__restrict__ gamma, int K, double *__restrict__ c) {
+  const double *gl = gamma + (size_t)e.lower * K, *gu = gamma + (size_t)e.upper * K;
+#pragma unroll
+  for (int k = 0; k < KC; ++k) c[k] = (k < K) ? (e.lower == e.upper ? gl[k] : gu[k] * e.upper_w + gl[k] * e.lower_w) : 0.0;
+}
+
+
+// One decision of one grid point for the two paths of a thread (LSV.cs:317-336): continuation value q . c, total NPV in
+// the reference's association ((-v*S)*DF - cost + (-consumed*S)*DF) + continuation - inventoryCost, strict-> argmax
+// (first maximum wins, SH.cs:206-221) and adj = -regressed + realised continuation (LSV.cs:330-332) where the realised
+// value is the WeightedAverage of the v_next rows (LSV.cs:296-302, 828-836; an exact grid hit has weights (1,0) and
+// reproduces the row bit for bit).
+template <int KP>
+__device__ __forceinline__ void evaluate_decision(bool first, const DecisionA &da, double upper_w, const double *__restrict__ c,
+                                                  const double2 lo, const double2 up, const double (&q0)[KP], const double (&q1)[KP],
+                                                  double price0, double price1, double df, double inv_cost, double &best0,
+                                                  double &best1, double &adj0, double &adj1) {
+  double cont0 = q0[0] * c[0], cont1 = q1[0] * c[0];
+#pragma unroll
+  for (int k = 1; k < KP; ++k) {
+    cont0 = __fma_rn(q0[k], c[k], cont0);
+    cont1 = __fma_rn(q1[k], c[k], cont1);
+  }
+  const double t0 = ((((da.neg_volume * price0) * df - da.cost_npv) + (da.neg_consumed * price0) * df) + cont0) - inv_cost;
+  const double t1 = ((((da.neg_volume * price1) * df - da.cost_npv) + (da.neg_consumed * price1) * df) + cont1) - inv_cost;
+  const double a0 = -cont0 + (up.x * upper_w + lo.x * da.lower_w);
+  const double a1 = -cont1 + (up.y * upper_w + lo.y * da.lower_w);
+  if (first || t0 > best0) {
+    best0 = t0;
+    adj0 = a0;
+  }
+  if (first || t1 > best1) {
+    best1 = t1;
+    adj1 = a1;
+  }
+}
+
+}  // namespace lsmc

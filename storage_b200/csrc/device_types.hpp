@@ -46,7 +46,10 @@ struct BackwardStepArgs {
   const double *q_prev; // [K][pitch] basis rows of period-1 for the regression sums (NULL with accumulate: mean mode)
   int accumulate;       // 0: no further regression (period 0)
   double *partials;     // [num_tiles][G][acc] per-tile sums of q_prev[k] * v_this[g]
-  int subtiles_per_cta; // inventory-grid sub-tiles (of kMaxGridTile points) one CTA sweeps
+  int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring kernel)
+  // ring kernel only: rows of v_next needed by each group of 8 grid points, and the ring size in rows
+  const int32_t *win_lo, *win_hi;
+  int ring_rows;
   // terminal mode: v_this[g][n] = TerminalStorageNpv(spot[n], grid_this[g]) instead of the decision step
   int terminal_mode;
   const double *grid_this;  // [G]

@@ -19,6 +19,7 @@
 #include <cstdint>
 #include <cstdlib>
 
+#include "backward_common.cuh"
 #include "dd.cuh"
 #include "device_types.hpp"
 #include "kernels.hpp"
@@ -278,26 +279,11 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
 // The regression sums of the next backward step, sum_n q_prev[n][k] * V[g][n], are a dense skinny FP64 GEMM
 // (K x paths) x (paths x grid points).  Each warp runs it on the tensor cores (mma.sync m8n8k4 f64) over its own 64
 // paths from a warp-private shared-memory tile, 8 grid points at a time; warps are combined in a fixed order.
-struct __align__(16) DecisionA {  // one LDS.128 each
-  double neg_volume, neg_consumed, cost_npv, lower_w;
-};
-struct __align__(16) DecisionB {
-  double upper_w;
-  long long lower_off, upper_off;  // row offsets into v_next, in doubles
-  double pad;
-};
-
-constexpr int kWarpPaths = 32 * kPathsPerThread;  // 64 paths per warp
-constexpr int kTilePitch = kWarpPaths + 4;        // row pitch of the warp-private tiles: conflict-free fragment loads
-
-__device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-               : "+d"(c0), "+d"(c1)
-               : "d"(a), "d"(b));
-}
-
+#ifndef LSMC_BACKWARD_MIN_CTAS
+#define LSMC_BACKWARD_MIN_CTAS 4
+#endif
 template <int KP>
-__global__ void __launch_bounds__(kThreads) backward_step_kernel(BackwardStepArgs a) {
+__global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_step_kernel(BackwardStepArgs a) {
   constexpr int ACC = KP <= 8 ? 8 : 16;       // width of a stored partial-sum row
   constexpr int KC = (KP + 1) & ~1;           // coefficient row padded to an even length (16-byte rows)
   constexpr int TG = kMaxGridTile;

@@ -51,6 +51,9 @@ void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t 
 void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream);
 void launch_backward_step(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 void launch_basis(const BasisArgs &a, cudaStream_t stream);
+// TMA-staged variant (backward_ring.cu); gsplit CTAs per path tile, each sweeping a.subtiles_per_cta groups of 8 grid points
+size_t backward_ring_smem_bytes(int KP, int D, int ring_rows);
+void launch_backward_ring(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream);
 // out[i] = sum over ranks r of all[r][i] (rank order); mean_mode: component 0 of every K-vector divided by total_paths, rest 0

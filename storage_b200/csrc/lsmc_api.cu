@@ -6,6 +6,8 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <climits>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -95,7 +97,9 @@ struct lsmc_handle {
   DeviceBuffer<double> v_a, v_b, grids, gamma, rinv, partials, gram_partials, inv_cost, pv, final_inv, step_sums, step_totals,
       block_sums, gather_buf, qbuf[2], ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
   DeviceBuffer<DevDecision> decisions;
-  DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
+  DeviceBuffer<int32_t> num_decisions, d_powers, error_flag, win_lo, win_hi;
+  std::vector<size_t> window_offset;  // per period: first group in win_lo / win_hi
+  std::vector<int> ring_rows;         // per period: ring size the TMA-staged kernel needs (0: use the direct-load kernel)
   DeviceBuffer<DevPeriodParams> period_params;
   DeviceBuffer<BasisSpec> gram_specs;
   DeviceBuffer<double> panels[7];  // inventory, volume, consumed, loss, net volume, pv, decision index
@@ -292,6 +296,44 @@ void build_device_tables(lsmc_handle *h) {
   h->num_decisions.upload(nd);
   h->inv_cost.upload(invc);
 
+  // Row windows of the next period's value slab that each group of 8 grid points reads (backward_ring.cu).  The ring
+  // variant needs the windows to slide upwards and to fit in shared memory; otherwise the period uses direct loads.
+  {
+    constexpr int kGroup = 8, kMaxRing = 40;
+    // The TMA-staged variant is correct but currently slower than the direct-load kernel on B200 (8 warps/SM, see
+    // profiles/r01_backward_ring.txt); it is opt-in until it wins.
+    const char *ring_env = std::getenv("LSMC_RING");
+    const bool no_ring = !(ring_env && std::atoi(ring_env) != 0);
+    std::vector<int32_t> lo_all, hi_all;
+    h->window_offset.assign(P, 0);
+    h->ring_rows.assign(P, 0);
+    for (int p = 0; p < P; ++p) {
+      const PeriodTables &pt = h->tables.periods[p];
+      const int G = (int)pt.grid.size(), groups = (G + kGroup - 1) / kGroup;
+      h->window_offset[p] = lo_all.size();
+      std::vector<int32_t> lo(groups, INT32_MAX), hi(groups, -1);
+      for (int g = 0; g < G; ++g)
+        for (int d2 = 0; d2 < pt.num_decisions[g]; ++d2) {
+          const DecisionEntry &e = pt.decisions[(size_t)g * D + d2];
+          lo[g / kGroup] = std::min(lo[g / kGroup], e.lower);
+          hi[g / kGroup] = std::max(hi[g / kGroup], e.upper);
+        }
+      bool ok = !no_ring;
+      int need = 0;
+      for (int j = 0; j < groups; ++j) {
+        if (j + 1 < groups && lo[j + 1] < lo[j]) ok = false;  // window must slide upwards
+        const int next_hi = j + 1 < groups ? std::max(hi[j + 1], hi[j]) : hi[j];
+        need = std::max(need, next_hi - lo[j] + 1);
+      }
+      if (need > kMaxRing) ok = false;
+      h->ring_rows[p] = ok ? std::max(need, 2) : 0;
+      lo_all.insert(lo_all.end(), lo.begin(), lo.end());
+      hi_all.insert(hi_all.end(), hi.begin(), hi.end());
+    }
+    h->win_lo.upload(lo_all);
+    h->win_hi.upload(hi_all);
+  }
+
   std::vector<double> grids((size_t)(P + 1) * Gmax, 0.0);
   for (int p = 0; p <= P; ++p) std::copy(h->tables.periods[p].grid.begin(), h->tables.periods[p].grid.end(), grids.begin() + (size_t)p * Gmax);
   h->grids.upload(grids);
@@ -373,6 +415,13 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   };
   check_cancel();
 
+  const bool debug_sync = std::getenv("LSMC_DEBUG_SYNC") != nullptr;
+  auto dbg = [&](const char *what, int p) {
+    if (!debug_sync) return;
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) throw CudaFailure(std::string(what) + " (period " + std::to_string(p) + ") failed: " + cudaGetErrorString(e));
+  };
   Timer t_pinv(st), t_back(st), t_fwd(st), t_dev(st);
   struct EventList {
     std::vector<cudaEvent_t> ev;
@@ -421,8 +470,10 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     ca.partials = h->gram_partials.ptr;
     ca.rinv = h->rinv.ptr + (size_t)first_reg * K * K * 2;
     ca.error_flag = h->error_flag.ptr;
+    dbg("gram_kernel", -1);
     launch_cholesky(ca, num_slots, st);
     launches++;
+    dbg("cholesky_kernel", -1);
   }
   t_pinv.stop();
 
@@ -445,6 +496,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     b.q_out = q_buffer(period);
     launch_basis(b, st);
     launches++;
+    dbg("basis_kernel", period);
   };
   auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this) {
     const PeriodTables &pt = h->tables.periods[p];
@@ -481,15 +533,26 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.q_prev = has_basis(p - 1) ? q_buffer(p - 1) : nullptr;
     a.partials = h->partials.ptr;
     // split the inventory grid over several CTAs only when there are too few path tiles to fill the GPU
-    const int subtiles = (a.G + kMaxGridTile - 1) / kMaxGridTile;
-    const int64_t slots = (int64_t)sm_count * 5;
+    const bool ring = !terminal && h->ring_rows[p] > 0;
+    const int sub_size = ring ? 8 : kMaxGridTile;
+    const int subtiles = (a.G + sub_size - 1) / sub_size;
+    const int64_t slots = (int64_t)sm_count * (ring ? 2 : 4);
     int gsplit = (int)std::min<int64_t>(subtiles, std::max<int64_t>(1, (4 * slots + num_tiles - 1) / num_tiles));
+    if (const char *forced = std::getenv("LSMC_GSPLIT")) gsplit = std::max(1, std::min(subtiles, std::atoi(forced)));  // test hook
     a.subtiles_per_cta = (subtiles + gsplit - 1) / gsplit;
     gsplit = (subtiles + a.subtiles_per_cta - 1) / a.subtiles_per_cta;
     if (!terminal) cudaEventRecord(step_events[2 * p], st);
-    launch_backward_step(a, gsplit, num_tiles, st);
+    if (ring) {
+      a.win_lo = h->win_lo.ptr + h->window_offset[p];
+      a.win_hi = h->win_hi.ptr + h->window_offset[p];
+      a.ring_rows = h->ring_rows[p];
+      launch_backward_ring(a, gsplit, num_tiles, st);
+    } else {
+      launch_backward_step(a, gsplit, num_tiles, st);
+    }
     if (!terminal) cudaEventRecord(step_events[2 * p + 1], st);
     launches++;
+    dbg(ring ? "backward_ring_kernel" : "backward_step_kernel", p);
     return (int)num_tiles;
   };
   auto reduce_gamma = [&](int p, int G_next, int num_chunks) {
@@ -581,6 +644,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.error_flag = h->error_flag.ptr;
   launch_forward(fa, fwd_ctas, st);
   launches++;
+  dbg("forward_kernel", -1);
   launch_reduce_step_sums(h->step_sums.ptr, P, fwd_ctas, sums_width, h->step_totals.ptr, st);
   launches++;
   t_fwd.stop();
@@ -722,7 +786,7 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     h->sim_rows = h->P + 1 - h->first_sim;
     h->Gmax = h->tables.max_grid;
     h->D = h->tables.max_decisions;
-    h->pitch = (h->N + 31) / 32 * 32;
+    h->pitch = (h->N + kTilePaths - 1) / kTilePaths * kTilePaths;  // whole tiles: the TMA row copies never run off a row
     h->device = device;
 
     require_device(device);

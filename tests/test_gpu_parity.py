@@ -125,3 +125,21 @@ def test_single_period_storage():
 def test_larger_path_count_config1():
     """configs[1] nearer its size: 20,000 paths (the oracle's exact mode needs ~10 s here)."""
     check_case(cases.three_factor_ratchets(num_sims=20_000, num_days=60, seed=21, outages=False))
+
+
+@pytest.mark.parametrize("gsplit", ["1", "3"])
+def test_tma_ring_variant_of_backward_kernel(monkeypatch, gsplit):
+    """The opt-in backward kernel that stages the next period's value rows in a shared-memory ring with bulk TMA copies
+    (backward_ring.cu), with one CTA sweeping the whole grid (gsplit=1, exercises the double-buffered mbarriers) and with
+    the grid split over CTAs."""
+    monkeypatch.setenv("LSMC_RING", "1")
+    monkeypatch.setenv("LSMC_GSPLIT", gsplit)
+    check_case(cases.three_factor_ratchets(num_sims=1500, num_days=40, seed=13))
+    check_case(cases.simple_one_factor(num_sims=1009, num_days=30, seed=6))
+
+
+def test_grid_split_of_direct_kernel(monkeypatch):
+    """Direct-load backward kernel with one CTA sweeping all inventory-grid sub-tiles of its path tile (the layout used at
+    production path counts) instead of one sub-tile per CTA."""
+    monkeypatch.setenv("LSMC_GSPLIT", "1")
+    check_case(cases.three_factor_ratchets(num_sims=1500, num_days=40, seed=14))
