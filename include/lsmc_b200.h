@@ -236,6 +236,25 @@ lsmc_status lsmc_set_sims_device(lsmc_handle *h, int which, const double *spot, 
 lsmc_status lsmc_simulate(lsmc_handle *h, int which, const lsmc_multi_factor_params *params,
                           uint64_t seed, int antithetic, int64_t first_path_id);
 
+/* No counterpart in the reference.  The same simulation as lsmc_simulate (same draws for the same seed and path ids),
+ * for hosts that may not allocate device memory while they run: services that reserve all their GPU memory at start-up
+ * because a later cudaMalloc can fail on a fragmented heap and synchronises the whole device, and hosts that own the
+ * GPU heap through an arena of their own.  Nothing is allocated or freed on the device: the caller passes the output
+ * buffers (device pointers: spot [rows][num_sims] and one [rows][num_sims] buffer per factor, rows = num_periods + 1 -
+ * (current_period_is_active ? 1 : 0)), and the per-period parameter table the kernel needs lives in a fixed array inside
+ * the library.  That array holds at most lsmc_simulate_noalloc_max_periods() (2048) simulated periods — a longer horizon
+ * is rejected with LSMC_ERR_ARGUMENT — and occupies about 1.3 MB on every GPU that has the library loaded, until exit.
+ * All calls share it and it keeps the previous call's rows (each call rewrites every row it reads, so nothing needs
+ * clearing): calls whose GPU work overlaps, on different streams or from different host threads, corrupt each other's
+ * table and must be serialised by the caller.  The first call on a device looks up the array's device address; make that
+ * first call before starting any stream capture.  The kernel runs on `cuda_stream` (a cudaStream_t, NULL = default
+ * stream) and the call returns after it has finished.  Errors: message via lsmc_last_error(NULL). */
+lsmc_status lsmc_simulate_noalloc(int device, const lsmc_multi_factor_params *params, int32_t num_periods,
+                                  int32_t current_period_is_active, const double *forward_price, int64_t num_sims, uint64_t seed,
+                                  int antithetic, int64_t first_path_id, double *spot_device, double *const *factors_device,
+                                  void *cuda_stream);
+int32_t lsmc_simulate_noalloc_max_periods(void);
+
 /* Replaces the compute half of Calculate (LSV.cs:100-657): backward induction, forward simulation,
  * trigger prices, NPV.  `cancel` (may be NULL) is polled once per backward and forward step like
  * CancellationToken.ThrowIfCancellationRequested (LSV.cs:345,521). */

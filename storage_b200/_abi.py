@@ -138,6 +138,10 @@ SYMBOLS = [
     ("lsmc_set_sims", C.c_int, [_H, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
     ("lsmc_set_sims_device", C.c_int, [_H, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
     ("lsmc_simulate", C.c_int, [_H, C.c_int, C.POINTER(lsmc_multi_factor_params), C.c_uint64, C.c_int, C.c_int64]),
+    ("lsmc_simulate_noalloc", C.c_int,
+     [C.c_int, C.POINTER(lsmc_multi_factor_params), C.c_int32, C.c_int32, c_double_p, C.c_int64, C.c_uint64, C.c_int, C.c_int64,
+      C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p]),
+    ("lsmc_simulate_noalloc_max_periods", C.c_int32, []),
     ("lsmc_run", C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("lsmc_num_sim_periods", C.c_int32, [_H]),
     ("lsmc_num_periods", C.c_int32, [_H]),

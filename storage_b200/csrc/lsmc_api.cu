@@ -892,6 +892,21 @@ lsmc_status lsmc_simulate(lsmc_handle *h, int which, const lsmc_multi_factor_par
   }
 }
 
+lsmc_status lsmc_simulate_noalloc(int device, const lsmc_multi_factor_params *params, int32_t num_periods, int32_t current_period_is_active,
+                                  const double *forward_price, int64_t num_sims, uint64_t seed, int antithetic, int64_t first_path_id,
+                                  double *spot_device, double *const *factors_device, void *cuda_stream) {
+  try {
+    if (!params) throw Error(LSMC_ERR_ARGUMENT, "modelParameters is null");
+    simulate_multi_factor_noalloc(device, *params, num_periods, current_period_is_active ? 1 : 0, forward_price, num_sims, seed,
+                                  antithetic != 0, first_path_id, spot_device, factors_device, static_cast<cudaStream_t>(cuda_stream));
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(nullptr, e);
+  }
+}
+
+int32_t lsmc_simulate_noalloc_max_periods(void) { return simulate_noalloc_max_periods(); }
+
 lsmc_status lsmc_run(lsmc_handle *h, lsmc_progress_fn progress, void *user, const volatile int *cancel) {
   if (!h) return LSMC_ERR_ARGUMENT;
   try {
