@@ -611,15 +611,17 @@ class LsmcStorageValuation:
             model, num_sims = spec[1], spec[2]
             num_factors = model.NumFactors
         flat = FlatProblem(p, num_sims, num_factors, extra_flags=_abi.LSMC_RETURN_DECISION_INDEX if keep_decisions else 0)
+        if spec[0] == "panels":  # CheckSpotSim (LVP.cs:219-231): host-side, before any device call
+            for name, sims in (("regressionSpotSim", reg), ("valuationSpotSim", val)):
+                have = set(sims.SimulatedPeriods)
+                for sp in flat.sim_periods:
+                    if sp not in have:
+                        raise ArgumentException(f"{name} does not contain simulations for period {sp}.")
         h = Handle(flat, self._device)
         try:
             lib = h.lib
             if spec[0] == "panels":
-                for name, sims, which in (("regressionSpotSim", reg, 0), ("valuationSpotSim", val, 1)):
-                    have = set(sims.SimulatedPeriods)
-                    for sp in flat.sim_periods:  # CheckSpotSim (LVP.cs:219-231)
-                        if sp not in have:
-                            raise ArgumentException(f"{name} does not contain simulations for period {sp}.")
+                for sims, which in ((reg, 0), (val, 1)):
                     rows = sims.rows_for(flat.sim_periods)
                     h.set_sims(which, sims.SpotPriceSims[rows], [f[rows] for f in sims.FactorSims])
             else:
