@@ -190,6 +190,8 @@ def run_gpu(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n = args.sims
     params, model = build_params(n, args.days, args.grid)
@@ -201,18 +203,23 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    comm_id = {}
+
     def join_ranks(handle):
+        """Rank 0 draws a communicator id once, torch.distributed carries it to the other ranks; every handle then joins
+        with the same id (the library creates the NCCL communicator on first use and shares it afterwards)."""
         if world == 1:
             return
-        ident = torch.zeros(_abi.LSMC_COMM_ID_BYTES, dtype=torch.uint8)
-        if rank == 0:
-            buf = (C.c_ubyte * _abi.LSMC_COMM_ID_BYTES)()
-            handle.check(lib.lsmc_comm_unique_id(buf))
-            ident = torch.tensor(list(buf), dtype=torch.uint8)
-        ident = ident.cuda()
-        dist.broadcast(ident, 0)
-        raw = bytes(ident.cpu().tolist())
-        handle.check(lib.lsmc_comm_init(handle.h, raw, rank, world, n * world))
+        if "raw" not in comm_id:
+            ident = torch.zeros(_abi.LSMC_COMM_ID_BYTES, dtype=torch.uint8)
+            if rank == 0:
+                buf = (C.c_ubyte * _abi.LSMC_COMM_ID_BYTES)()
+                handle.check(lib.lsmc_comm_unique_id(buf))
+                ident = torch.tensor(list(buf), dtype=torch.uint8)
+            ident = ident.cuda()
+            dist.broadcast(ident, 0)
+            comm_id["raw"] = bytes(ident.cpu().tolist())
+        handle.check(lib.lsmc_comm_init(handle.h, comm_id["raw"], rank, world, n * world))
 
     def open_handle():
         """Everything a Calculate call does before the run: descriptor flattening, table build, device buffers, simulation."""

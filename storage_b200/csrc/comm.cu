@@ -6,6 +6,8 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -56,10 +58,14 @@ void nccl_ok(ncclResult_t r, const char *what) {
 
 static_assert(sizeof(ncclUniqueId) <= LSMC_COMM_ID_BYTES, "LSMC_COMM_ID_BYTES too small for ncclUniqueId");
 
+// Communicators are expensive to create (~1 s) and a host typically runs many valuations on the same set of ranks: a
+// communicator is created once per unique id and shared by every handle that joins with that id (kept until exit).
+std::mutex g_comm_mutex;
+std::map<std::string, ncclComm_t> g_comms;
+
 }  // namespace
 
 Comm::~Comm() {
-  if (nccl_comm_) nccl().CommDestroy(static_cast<ncclComm_t>(nccl_comm_));
   if (d_send_) cudaFree(d_send_);
   if (d_recv_) cudaFree(d_recv_);
 }
@@ -82,9 +88,15 @@ void Comm::init(const void *id, int rank, int world, int64_t total_sims) {
   if (!id) throw Error(LSMC_ERR_ARGUMENT, "communicator id is null");
   ncclUniqueId uid;
   std::memcpy(&uid, id, sizeof(uid));
-  ncclComm_t comm;
-  nccl_ok(nccl().CommInitRank(&comm, world, uid, rank), "ncclCommInitRank");
-  nccl_comm_ = comm;
+  const std::string key(reinterpret_cast<const char *>(&uid), sizeof(uid));
+  std::lock_guard<std::mutex> lock(g_comm_mutex);
+  auto it = g_comms.find(key);
+  if (it == g_comms.end()) {
+    ncclComm_t comm;
+    nccl_ok(nccl().CommInitRank(&comm, world, uid, rank), "ncclCommInitRank");
+    it = g_comms.emplace(key, comm).first;
+  }
+  nccl_comm_ = it->second;
 }
 
 void Comm::ensure_staging(size_t count) {
