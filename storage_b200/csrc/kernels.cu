@@ -282,13 +282,15 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
 #ifndef LSMC_BACKWARD_MIN_CTAS
 #define LSMC_BACKWARD_MIN_CTAS 4
 #endif
-template <int KP>
+// DFIX: decision-table row width when it is the usual 3 (no extra decisions) so the table indexing folds at compile time;
+// 0 = run-time width.
+template <int KP, int DFIX>
 __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_step_kernel(BackwardStepArgs a) {
   constexpr int ACC = KP <= 8 ? 8 : 16;       // width of a stored partial-sum row
   constexpr int KC = (KP + 1) & ~1;           // coefficient row padded to an even length (16-byte rows)
   constexpr int TG = kMaxGridTile;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int K = a.K, D = a.D;
+  const int K = a.K, D = DFIX ? DFIX : a.D;
   // dynamic smem: decA [TG][D] | decB [TG][D] | coef [TG][D][KC] | vtile [kWarps][8][pitch] | qtile [kWarps][ACC][pitch]
   //               | acc [kWarps][ACC][TG] | inv_cost [TG] | nd [TG]
   DecisionA *s_a = reinterpret_cast<DecisionA *>(smem_raw);
@@ -856,13 +858,18 @@ void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t sme
       cholesky_kernel<KP><<<grid, block, 0, stream>>>(*static_cast<const CholeskyArgs *>(args));
       break;
     case 2:
-      if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (static_cast<const BackwardStepArgs *>(args)->D == 3) {
+        if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        backward_step_kernel<KP, 3><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
+        break;
+      }
+      if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       {
         static int carve = -2;
         if (carve == -2) { const char *e = getenv("LSMC_CARVEOUT"); carve = e ? atoi(e) : -1; }
-        if (carve >= 0) cudaFuncSetAttribute(backward_step_kernel<KP>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        if (carve >= 0) cudaFuncSetAttribute(backward_step_kernel<KP, 0>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
       }
-      backward_step_kernel<KP><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
+      backward_step_kernel<KP, 0><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
       break;
     case 4:
       basis_kernel<KP><<<grid, block, 0, stream>>>(*static_cast<const BasisArgs *>(args));

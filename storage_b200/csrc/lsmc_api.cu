@@ -505,7 +505,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.N = N;
     a.pitch = h->pitch;
     a.G = (int)pt.grid.size();
-    a.D = terminal ? 1 : D;
+    a.D = terminal ? 3 : D;
     a.K = K;
     a.v_next = v_next;
     a.v_this = v_this;
@@ -787,6 +787,8 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     h->Gmax = h->tables.max_grid;
     h->D = h->tables.max_decisions;
     h->pitch = (h->N + kTilePaths - 1) / kTilePaths * kTilePaths;  // whole tiles: the TMA row copies never run off a row
+    if ((uint64_t)h->Gmax * (uint64_t)h->pitch >= (uint64_t)1 << 32)
+      throw Error(LSMC_ERR_ARGUMENT, "paths x inventory-grid points per device must stay below 2^32 (shard the paths over more GPUs)");
     h->device = device;
 
     require_device(device);
