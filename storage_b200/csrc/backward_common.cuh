@@ -70,4 +70,56 @@ __device__ __forceinline__ void evaluate_decision(bool first, const DecisionA &d
   }
 }
 
+// Rows of v_next one grid point needs: (lower, upper) per decision, both paths of the thread in one 16-byte load each.
+struct Rows {
+  double2 lo[3], up[3];
+};
+
+__device__ __forceinline__ void load_rows(const DecisionR *__restrict__ pb, int nd, const double *__restrict__ vbase, Rows &r) {
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (d < nd) {
+      r.lo[d] = *reinterpret_cast<const double2 *>(vbase + pb[d].lower_off);
+      r.up[d] = *reinterpret_cast<const double2 *>(vbase + pb[d].upper_off);
+    }
+  }
+}
+
+// One grid point with at most 3 decisions for the thread's two paths, its v_next rows already in registers.
+template <int KP, int KC>
+__device__ __forceinline__ void point(const DecisionA *__restrict__ pa, const DecisionR *__restrict__ pb, const double *__restrict__ pc,
+                                      int nd, double inv_cost, const Rows &r, const double (&q0)[KP], const double (&q1)[KP],
+                                      double price0, double price1, double df, double &v0, double &v1) {
+  double best0 = 0.0, best1 = 0.0, adj0 = 0.0, adj1 = 0.0;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (d < nd) {
+      const DecisionA da = pa[d];
+      evaluate_decision<KP>(d == 0, da, pb[d].upper_w, pc + d * KC, r.lo[d], r.up[d], q0, q1, price0, price1, df, inv_cost, best0,
+                            best1, adj0, adj1);
+    }
+  }
+  v0 = best0 + adj0;  // LSV.cs:333
+  v1 = best1 + adj1;
+}
+
+// Any number of decisions (ExtraDecisions > 0): rows are loaded as they are needed.
+template <int KP, int KC>
+__device__ __forceinline__ void point_generic(const DecisionA *__restrict__ pa, const DecisionR *__restrict__ pb,
+                                              const double *__restrict__ pc, int nd, double inv_cost, const double *__restrict__ vbase,
+                                              const double (&q0)[KP], const double (&q1)[KP], double price0, double price1, double df,
+                                              double &v0, double &v1) {
+  double best0 = 0.0, best1 = 0.0, adj0 = 0.0, adj1 = 0.0;
+  for (int d = 0; d < nd; ++d) {
+    const DecisionA da = pa[d];
+    const DecisionR db = pb[d];
+    const double2 lo = *reinterpret_cast<const double2 *>(vbase + db.lower_off);
+    const double2 up = *reinterpret_cast<const double2 *>(vbase + db.upper_off);
+    evaluate_decision<KP>(d == 0, da, db.upper_w, pc + (size_t)d * KC, lo, up, q0, q1, price0, price1, df, inv_cost, best0, best1, adj0,
+                          adj1);
+  }
+  v0 = best0 + adj0;
+  v1 = best1 + adj1;
+}
+
 }  // namespace lsmc

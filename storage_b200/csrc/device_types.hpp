@@ -31,6 +31,7 @@ struct BackwardStepArgs {
   int64_t N;            // paths on this device
   int64_t pitch;        // row pitch of the V and Q buffers, in doubles
   int G;                // grid points of this period
+  int Gn;               // grid points of the next period (rows of v_next)
   int D;                // max decisions (row width of the decision table)
   int K;                // basis functions
   const double *v_next; // [Gn][pitch]

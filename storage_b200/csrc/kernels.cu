@@ -279,6 +279,12 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
 // The regression sums of the next backward step, sum_n q_prev[n][k] * V[g][n], are a dense skinny FP64 GEMM
 // (K x paths) x (paths x grid points).  Each warp runs it on the tensor cores (mma.sync m8n8k4 f64) over its own 64
 // paths from a warp-private shared-memory tile, 8 grid points at a time; warps are combined in a fixed order.
+#ifndef LSMC_PF_DIST
+#define LSMC_PF_DIST 4
+#endif
+#ifndef LSMC_PF_L1
+#define LSMC_PF_L1 0
+#endif
 #ifndef LSMC_BACKWARD_MIN_CTAS
 #define LSMC_BACKWARD_MIN_CTAS 4
 #endif
@@ -294,7 +300,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_ste
   // dynamic smem: decA [TG][D] | decB [TG][D] | coef [TG][D][KC] | vtile [kWarps][8][pitch] | qtile [kWarps][ACC][pitch]
   //               | acc [kWarps][ACC][TG] | inv_cost [TG] | nd [TG]
   DecisionA *s_a = reinterpret_cast<DecisionA *>(smem_raw);
-  DecisionB *s_b = reinterpret_cast<DecisionB *>(s_a + (size_t)TG * D);
+  DecisionR *s_b = reinterpret_cast<DecisionR *>(s_a + (size_t)TG * D);
   double *s_coef = reinterpret_cast<double *>(s_b + (size_t)TG * D);
   double *s_vtile = s_coef + (size_t)TG * D * KC;
   double *s_qtile = s_vtile + (size_t)kWarps * 8 * kTilePitch;
@@ -351,6 +357,8 @@ __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_ste
   const double df = a.settle_df;
   const int sub_begin = blockIdx.x * a.subtiles_per_cta;
   const int sub_end = min(sub_begin + a.subtiles_per_cta, (a.G + TG - 1) / TG);
+  const double *vbase = a.v_next + c0;  // this thread's two columns of every v_next row
+  const uint32_t last_row_off = (uint32_t)(a.Gn > 0 ? a.Gn - 1 : 0) * (uint32_t)a.pitch;
 
   for (int sub = sub_begin; sub < sub_end; ++sub) {
     const int g0 = sub * TG;
@@ -363,11 +371,8 @@ __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_ste
         if (i - g * D < a.num_decisions[g0 + g]) {
           const DevDecision e = a.decisions[(size_t)g0 * D + i];
           s_a[i] = DecisionA{-e.volume, -e.consumed, e.cost_npv, e.lower_w};
-          s_b[i] = DecisionB{e.upper_w, (long long)e.lower * a.pitch, (long long)e.upper * a.pitch, 0.0};
-          double *c = s_coef + (size_t)i * KC;
-          const double *gl = a.gamma + (size_t)e.lower * K, *gu = a.gamma + (size_t)e.upper * K;
-#pragma unroll
-          for (int k = 0; k < KC; ++k) c[k] = (k < K) ? (e.lower == e.upper ? gl[k] : gu[k] * e.upper_w + gl[k] * e.lower_w) : 0.0;
+          s_b[i] = DecisionR{e.upper_w, (uint32_t)e.lower * (uint32_t)a.pitch, (uint32_t)e.upper * (uint32_t)a.pitch};
+          fold_coefficients<KC>(e, a.gamma, K, s_coef + (size_t)i * KC);
         }
       }
       for (int i = threadIdx.x; i < gcount; i += blockDim.x) {
@@ -377,118 +382,85 @@ __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_ste
     }
     __syncthreads();
 
-    double2 pre_lo[3], pre_up[3];  // v_next rows of the next grid point to evaluate (software prefetch, D <= 3 only)
-#pragma unroll
-    for (int d = 0; d < 3; ++d) pre_lo[d] = pre_up[d] = make_double2(0.0, 0.0);
-    if (!a.terminal_mode && D <= 3) {
-#pragma unroll
-      for (int d = 0; d < 3; ++d) {
-        if (d < s_nd[0]) {
-          const DecisionB nb = s_b[d];
-          pre_lo[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.lower_off + c0);
-          pre_up[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.upper_off + c0);
+    // ---- sweep the sub-tile's grid points.  Everything that varies with g advances by pointer increments; the rows of
+    // v_next for grid point g+1 are requested before the arithmetic of grid point g (two row buffers used alternately).
+    const DecisionA *pa = s_a;
+    const DecisionR *pb = s_b;
+    const double *pc = s_coef;
+    double *vout = a.v_this + (size_t)g0 * a.pitch + n0;
+    Rows rows_a, rows_b;
+    const bool fast = !a.terminal_mode && DFIX == 3;
+    if (fast) load_rows(pb, s_nd[0], vbase, rows_a);
+    for (int g = 0; g < gcount; g += 2) {
+      double v0, v1, w0 = 0.0, w1 = 0.0;
+      const bool second = g + 1 < gcount;
+      if (fast) {
+#if LSMC_PF_DIST > 0
+        {
+          // The row window slides up about one row per grid point; the rows a few grid points ahead are still in HBM.
+          // Ask for them now so they are in cache when their turn comes (one 16-byte column per thread = whole lines per warp).
+          const uint32_t ahead = pb[s_nd[g] - 1].upper_off + (uint32_t)LSMC_PF_DIST * (uint32_t)a.pitch;
+          const double *pf = vbase + (ahead < last_row_off ? ahead : last_row_off);
+#if LSMC_PF_L1
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(pf + a.pitch < vbase + last_row_off ? pf + a.pitch : vbase + last_row_off));
+#else
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(pf));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(pf + a.pitch < vbase + last_row_off ? pf + a.pitch : vbase + last_row_off));
+#endif
         }
+#endif
+        if (second) load_rows(pb + 3, s_nd[g + 1], vbase, rows_b);
+        point<KP, KC>(pa, pb, pc, s_nd[g], s_inv_cost[g], rows_a, q0, q1, price0, price1, df, v0, v1);
+        if (g + 2 < gcount) load_rows(pb + 6, s_nd[g + 2], vbase, rows_a);
+        if (second) point<KP, KC>(pa + 3, pb + 3, pc + 3 * KC, s_nd[g + 1], s_inv_cost[g + 1], rows_b, q0, q1, price0, price1, df, w0, w1);
+      } else if (a.terminal_mode) {
+        // V_T[g][n] = TerminalStorageNpv(S_T[n], grid_T[g]) (LSV.cs:121-131)
+        const double inv = a.grid_this[g0 + g], inv2 = second ? a.grid_this[g0 + g + 1] : 0.0;
+        v0 = ((a.terminal[3] * (price0 * inv) + a.terminal[1] * price0) + a.terminal[2] * inv) + a.terminal[0];
+        v1 = ((a.terminal[3] * (price1 * inv) + a.terminal[1] * price1) + a.terminal[2] * inv) + a.terminal[0];
+        w0 = ((a.terminal[3] * (price0 * inv2) + a.terminal[1] * price0) + a.terminal[2] * inv2) + a.terminal[0];
+        w1 = ((a.terminal[3] * (price1 * inv2) + a.terminal[1] * price1) + a.terminal[2] * inv2) + a.terminal[0];
+      } else {
+        point_generic<KP, KC>(s_a + g * D, s_b + g * D, s_coef + (size_t)g * D * KC, s_nd[g], s_inv_cost[g], vbase, q0, q1, price0,
+                              price1, df, v0, v1);
+        if (second)
+          point_generic<KP, KC>(s_a + (g + 1) * D, s_b + (g + 1) * D, s_coef + (size_t)(g + 1) * D * KC, s_nd[g + 1], s_inv_cost[g + 1],
+                                vbase, q0, q1, price0, price1, df, w0, w1);
       }
-    }
-
-    for (int gg = 0; gg < gcount; gg += 8) {
-      const int gn = min(8, gcount - gg);
-      for (int gi = 0; gi < 8; ++gi) {
-        double v0 = 0.0, v1 = 0.0;
-        if (gi < gn) {
-          const int g = gg + gi;
-          if (a.terminal_mode) {
-            // V_T[g][n] = TerminalStorageNpv(S_T[n], grid_T[g]) (LSV.cs:121-131)
-            const double inv = a.grid_this[g0 + g];
-            v0 = ((a.terminal[3] * (price0 * inv) + a.terminal[1] * price0) + a.terminal[2] * inv) + a.terminal[0];
-            v1 = ((a.terminal[3] * (price1 * inv) + a.terminal[1] * price1) + a.terminal[2] * inv) + a.terminal[0];
-          } else {
-            const int nd = s_nd[g];
-            const double inv_cost = s_inv_cost[g];
-            double best0 = 0.0, best1 = 0.0, adj0 = 0.0, adj1 = 0.0;
-            auto evaluate = [&](int d, const double2 lo, const double2 up) {
-              const DecisionA da = s_a[g * D + d];
-              const double upper_w = s_b[g * D + d].upper_w;
-              const double *c = s_coef + (size_t)(g * D + d) * KC;
-              double cont0 = q0[0] * c[0], cont1 = q1[0] * c[0];
-#pragma unroll
-              for (int k = 1; k < KP; ++k) {
-                cont0 = __fma_rn(q0[k], c[k], cont0);
-                cont1 = __fma_rn(q1[k], c[k], cont1);
-              }
-              // LSV.cs:317-325, same association: ((-v*S)*DF - cost + (-consumed*S)*DF) + continuation - inventoryCost
-              const double t0 = ((((da.neg_volume * price0) * df - da.cost_npv) + (da.neg_consumed * price0) * df) + cont0) - inv_cost;
-              const double t1 = ((((da.neg_volume * price1) * df - da.cost_npv) + (da.neg_consumed * price1) * df) + cont1) - inv_cost;
-              // realised continuation value: WeightedAverage of the v_next rows (LSV.cs:296-302, 828-836); an exact grid
-              // hit has weights (1, 0) and reproduces the row bit for bit.  adj = -regressed + realised (LSV.cs:330-332)
-              const double a0 = -cont0 + (up.x * upper_w + lo.x * da.lower_w);
-              const double a1 = -cont1 + (up.y * upper_w + lo.y * da.lower_w);
-              if (d == 0 || t0 > best0) {  // strict >: first maximum wins (SH.cs:206-221)
-                best0 = t0;
-                adj0 = a0;
-              }
-              if (d == 0 || t1 > best1) {
-                best1 = t1;
-                adj1 = a1;
-              }
-            };
-            if (D <= 3) {
-              // common case (no extra decisions): the rows of v_next for this grid point were requested one grid point
-              // ago (pre_lo/pre_up); request the next grid point's rows before the arithmetic of this one
-              double2 cur_lo[3], cur_up[3];
-#pragma unroll
-              for (int d = 0; d < 3; ++d) {
-                cur_lo[d] = pre_lo[d];
-                cur_up[d] = pre_up[d];
-              }
-              const int gnext = g + 1;
-              if (gnext < gcount) {
-#pragma unroll
-                for (int d = 0; d < 3; ++d) {
-                  if (d < s_nd[gnext]) {
-                    const DecisionB nb = s_b[gnext * D + d];
-                    pre_lo[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.lower_off + c0);
-                    pre_up[d] = *reinterpret_cast<const double2 *>(a.v_next + nb.upper_off + c0);
-                  }
-                }
-              }
-#pragma unroll
-              for (int d = 0; d < 3; ++d)
-                if (d < nd) evaluate(d, cur_lo[d], cur_up[d]);
-            } else {
-              for (int d = 0; d < nd; ++d) {
-                const DecisionB db = s_b[g * D + d];
-                evaluate(d, *reinterpret_cast<const double2 *>(a.v_next + db.lower_off + c0),
-                         *reinterpret_cast<const double2 *>(a.v_next + db.upper_off + c0));
-              }
-            }
-            v0 = best0 + adj0;  // LSV.cs:333
-            v1 = best1 + adj1;
-          }
-          if (!valid0) v0 = 0.0;
-          if (!valid1) v1 = 0.0;
-          if (valid0) *reinterpret_cast<double2 *>(a.v_this + (size_t)(g0 + g) * a.pitch + n0) = make_double2(v0, v1);
-        }
-        if (a.accumulate) *reinterpret_cast<double2 *>(my_v + (size_t)gi * kTilePitch + 2 * lane) = make_double2(v0, v1);
+      if (!valid0) v0 = w0 = 0.0;
+      if (!valid1) v1 = w1 = 0.0;
+      if (valid0) {
+        *reinterpret_cast<double2 *>(vout) = make_double2(v0, v1);
+        if (second) *reinterpret_cast<double2 *>(vout + a.pitch) = make_double2(w0, w1);
       }
-
+      vout += 2 * a.pitch;
+      pa += 6;
+      pb += 6;
+      pc += 6 * KC;
       if (a.accumulate) {
-        // C[k][g] += sum over the warp's 64 paths of Q_prev[k][n] * V[g][n]: 16 k-steps of m8n8k4 per 8 basis rows
-        __syncwarp();
-        const int row = lane >> 2, col = lane & 3;
+        double *vt = my_v + (size_t)(g & 7) * kTilePitch + 2 * lane;
+        *reinterpret_cast<double2 *>(vt) = make_double2(v0, v1);
+        *reinterpret_cast<double2 *>(vt + kTilePitch) = make_double2(w0, w1);
+        if ((g & 7) == 6 || g + 2 >= gcount) {
+          // C[k][g] = sum over the warp's 64 paths of Q_prev[k][n] * V[g][n] for this group of 8 grid points (rows of the
+          // tile beyond the last grid point hold stale values; their columns of C are never read)
+          __syncwarp();
+          const int row = lane >> 2, col = lane & 3, gg = g & ~7;
 #pragma unroll
-        for (int mb = 0; mb < ACC; mb += 8) {
-          double acc0 = 0.0, acc1 = 0.0;
-          const double *qa = my_q + (size_t)(mb + row) * kTilePitch + col;
-          const double *vb = my_v + (size_t)row * kTilePitch + col;
+          for (int mb = 0; mb < ACC; mb += 8) {
+            double acc0 = 0.0, acc1 = 0.0;
+            const double *qa = my_q + (size_t)(mb + row) * kTilePitch + col;
+            const double *vb = my_v + (size_t)row * kTilePitch + col;
 #pragma unroll 4
-          for (int p = 0; p < kWarpPaths; p += 4) dmma_m8n8k4(acc0, acc1, qa[p], vb[p]);
-          // C fragment: row = basis index mb + lane/4, columns = grid points 2*(lane%4) + {0,1} of this group
-          double *dst = s_acc + ((size_t)warp * ACC + mb + row) * TG + gg + 2 * col;
-          dst[0] = acc0;
-          dst[1] = acc1;
+            for (int p = 0; p < kWarpPaths; p += 4) dmma_m8n8k4(acc0, acc1, qa[p], vb[p]);
+            // C fragment: row = basis index mb + lane/4, columns = grid points 2*(lane%4) + {0,1} of this group
+            double *dst = s_acc + ((size_t)warp * ACC + mb + row) * TG + gg + 2 * col;
+            dst[0] = acc0;
+            dst[1] = acc1;
+          }
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
 

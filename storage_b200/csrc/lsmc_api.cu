@@ -505,6 +505,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.N = N;
     a.pitch = h->pitch;
     a.G = (int)pt.grid.size();
+    a.Gn = terminal ? 0 : (int)h->tables.periods[p + 1].grid.size();
     a.D = terminal ? 3 : D;
     a.K = K;
     a.v_next = v_next;
