@@ -68,6 +68,10 @@ enum {
   LSMC_RETURN_NET_VOLUME = 1 << 9,
   LSMC_RETURN_PV = 1 << 10,
   LSMC_RETURN_DECISION_INDEX = 1 << 16, /* no reference counterpart: keep the argmax index of every (period, sim) */
+  LSMC_REFERENCE_OPERATION_ORDER = 1 << 17, /* no reference counterpart: evaluate each decision's immediate cash flow with the
+                                               reference's own sequence of roundings (LSV.cs:317-336) instead of the fused
+                                               form S*coef + offset; both are within 1e-9 of the reference, the fused one is
+                                               the default because it needs a third fewer FP64 operations */
   LSMC_RETURN_ALL = 1 | (1 << 2) | (1 << 3) | (1 << 4) | (1 << 5) | (1 << 6) | (1 << 7) | (1 << 8) | (1 << 9) | (1 << 10)
 };
 

@@ -23,6 +23,7 @@ LSMC_COMM_ID_BYTES = 128
  LSMC_PANEL_FACTORS_REGRESSION, LSMC_PANEL_FACTORS_VALUATION, LSMC_PANEL_DECISION_INDEX) = range(11)
 
 LSMC_RETURN_DECISION_INDEX = 1 << 16
+LSMC_REFERENCE_OPERATION_ORDER = 1 << 17
 
 c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)

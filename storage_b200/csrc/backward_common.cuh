@@ -103,6 +103,50 @@ __device__ __forceinline__ void point(const DecisionA *__restrict__ pa, const De
   v1 = best1 + adj1;
 }
 
+// Fused-payoff form of a decision.  The reference's five roundings of the immediate cash flow,
+// ((-v*S)*DF - cost) + (-consumed*S)*DF ... - inventoryCost, collapse into one FMA S*price_coef + offset with
+// price_coef = (-v - consumed)*DF and offset = -(cost + inventoryCost) folded per decision when the tables are staged, and
+// the value carried for the winning decision is payoff + realised continuation directly instead of
+// (payoff + regressed) + (realised - regressed).  Same real-number result; differs from the reference's roundings by a
+// few ulp of the payoff, far below the 1e-9 parity tolerance.  13 FP64 operations per decision and path instead of 20.
+struct __align__(16) DecisionF {
+  double price_coef, offset, lower_w, upper_w;
+};
+static_assert(sizeof(DecisionF) == sizeof(DecisionA), "the fused table re-uses the DecisionA slots");
+
+template <int KP, int KC>
+__device__ __forceinline__ void point_fused(const DecisionF *__restrict__ pf, const double *__restrict__ pc, int nd, const Rows &r,
+                                            const double (&q0)[KP], const double (&q1)[KP], double price0, double price1, double &v0,
+                                            double &v1) {
+  double best0 = 0.0, best1 = 0.0;
+  v0 = v1 = 0.0;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (d < nd) {
+      const DecisionF f = pf[d];
+      const double *c = pc + d * KC;
+      double cont0 = q0[0] * c[0], cont1 = q1[0] * c[0];
+#pragma unroll
+      for (int k = 1; k < KP; ++k) {
+        cont0 = __fma_rn(q0[k], c[k], cont0);
+        cont1 = __fma_rn(q1[k], c[k], cont1);
+      }
+      const double pay0 = __fma_rn(price0, f.price_coef, f.offset), pay1 = __fma_rn(price1, f.price_coef, f.offset);
+      const double t0 = pay0 + cont0, t1 = pay1 + cont1;  // what the argmax is taken over (LSV.cs:317-327)
+      const double w0 = pay0 + __fma_rn(r.up[d].x, f.upper_w, r.lo[d].x * f.lower_w);
+      const double w1 = pay1 + __fma_rn(r.up[d].y, f.upper_w, r.lo[d].y * f.lower_w);
+      if (d == 0 || t0 > best0) {
+        best0 = t0;
+        v0 = w0;
+      }
+      if (d == 0 || t1 > best1) {
+        best1 = t1;
+        v1 = w1;
+      }
+    }
+  }
+}
+
 // Any number of decisions (ExtraDecisions > 0): rows are loaded as they are needed.
 template <int KP, int KC>
 __device__ __forceinline__ void point_generic(const DecisionA *__restrict__ pa, const DecisionR *__restrict__ pb,

@@ -1,0 +1,393 @@
+// backward_sweep.cu — the backward-induction step (LSV.cs:240-338) for the usual three-decision table
+// (inject / hold / withdraw, no extra decisions).  kernels.cu keeps the general kernel (any table width, terminal step).
+//
+// Work layout.  A CTA owns 128 paths and a contiguous range of inventory-grid points.  Its 8 warps are 2 path groups x 4
+// grid slots: every lane owns two adjacent paths of its group (double2 loads), and the four warps of a group take the grid
+// points g = slot (mod 4).  The rows of v_next a decision interpolates between slide upwards with g, so four warps working
+// on neighbouring grid points of the same paths share one sliding window of rows: the window of a group is a few KB and
+// stays in L1, where the same 16 warps sweeping their own path tiles would each keep their own window and spill to L2.
+//
+// All sim-independent operands of a grid point — decision payoffs, interpolation weights and row offsets, and the
+// regression coefficients with the next-grid interpolation folded in — are prepared once per step by fold_tables_kernel
+// into one record per grid point; the sweep kernel copies records into a shared-memory ring with cp.async, two sub-tiles
+// ahead, so no warp waits for them.
+//
+// The regression sums of the next backward step, sum_n q_prev[k][n] * V[g][n] (the right-hand side of LSV.cs:199-212 in
+// the orthonormal basis), are a skinny FP64 GEMM run on the tensor path (mma.sync m8n8k4 f64) once per block of 8 grid
+// points: the warps publish their V values to a double-buffered shared tile, meet at one barrier, and each multiplies its
+// 16-path slice, with its slice of q_prev held in registers.  Slices are combined in a fixed order: deterministic.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdlib>
+
+#include "backward_common.cuh"
+#include "device_types.hpp"
+#include "kernels.hpp"
+
+#ifndef LSMC_SWEEP_PF
+#define LSMC_SWEEP_PF 8  // rows ahead of the window that are requested into L2
+#endif
+#ifndef LSMC_SWEEP_MIN_CTAS
+#define LSMC_SWEEP_MIN_CTAS 2
+#endif
+
+namespace lsmc {
+
+namespace {
+
+constexpr int kSweepThreads = 256;
+constexpr int kSweepWarps = kSweepThreads / 32;
+constexpr int kSlots = 4;                             // warps sharing a path group, one grid point each (mod 4)
+constexpr int kGroupPaths = 64;                       // 32 lanes x double2
+constexpr int kBlockG = 8;                            // grid points per block = n of the m8n8k4 tile
+constexpr int kTabSub = 32;                           // records per staged sub-tile
+constexpr int kTabRing = 2 * kTabSub;                 // records resident in shared memory
+constexpr int kVPitch = kSweepTilePaths + 4;          // conflict-free fragment loads (pitch = 8 banks mod 32)
+static_assert(kSweepTilePaths == (kSweepWarps / kSlots) * kGroupPaths, "two path groups per CTA");
+
+// Everything one grid point needs that does not depend on the path.  Always three decisions: a grid point with fewer
+// carries copies of its first decision in the unused slots, which can never win the strict > comparison (SH.cs:206-221),
+// so the sweep has no per-decision branches.
+template <int KC>
+struct __align__(16) PointTable {
+  DecisionA a[3];     // fused payoff: {price_coef, offset, lower_w, upper_w} (DecisionF); reference order: DecisionA
+  double c[3][KC];    // regression coefficients with the next-grid interpolation folded in
+  double upper_w[3];  // reference order only
+  double inv_cost;    // reference order only
+  uint32_t lower_row[3], upper_row[3];  // rows of v_next the decision interpolates between
+  uint32_t ahead_row;                   // row to request into L2 now: a few rows above this point's window
+  int32_t nd;
+};
+
+__device__ __forceinline__ void cp_async_16(void *dst_smem, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+template <int KC>
+__global__ void fold_tables_kernel(FoldArgs f) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= f.G * 3) return;
+  const int g = i / 3, d = i - 3 * g;
+  PointTable<KC> *t = reinterpret_cast<PointTable<KC> *>(f.out) + g;
+  const int nd = f.num_decisions[g];
+  const double inv = f.inventory_cost[g];
+  if (d == 0) {
+    t->inv_cost = inv;
+    t->nd = nd;
+    const uint32_t top = (uint32_t)f.decisions[(size_t)g * 3 + (nd - 1)].upper + (uint32_t)LSMC_SWEEP_PF;
+    t->ahead_row = f.Gn > 0 ? min(top, (uint32_t)(f.Gn - 1)) : 0u;
+  }
+  const DevDecision e = f.decisions[(size_t)g * 3 + (d < nd ? d : 0)];
+  if (f.fused_payoff)
+    t->a[d] = DecisionA{(-e.volume - e.consumed) * f.settle_df, -(e.cost_npv + inv), e.lower_w, e.upper_w};
+  else
+    t->a[d] = DecisionA{-e.volume, -e.consumed, e.cost_npv, e.lower_w};
+  t->upper_w[d] = e.upper_w;
+  t->lower_row[d] = (uint32_t)e.lower;
+  t->upper_row[d] = (uint32_t)e.upper;
+  fold_coefficients<KC>(e, f.gamma, f.K, t->c[d]);
+}
+
+// base + row * pitch_bytes as one IMAD.WIDE (the compiler otherwise widens the 32-bit pitch and adds a zero high word)
+__device__ __forceinline__ const char *row_address(const char *base, uint32_t row, uint32_t pitch_bytes) {
+  const char *p;
+  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(p) : "r"(row), "r"(pitch_bytes), "l"(base));
+  return p;
+}
+// 16-byte load of this thread's two columns of row `row` (v_next is read-only for the whole launch)
+__device__ __forceinline__ double2 load_row(const char *base, uint32_t row, uint32_t pitch_bytes) {
+  double2 v;
+  asm("{\n\t.reg .u64 p;\n\tmad.wide.u32 p, %2, %3, %4;\n\tld.global.v2.f64 {%0, %1}, [p];\n\t}"
+      : "=d"(v.x), "=d"(v.y)
+      : "r"(row), "r"(pitch_bytes), "l"(base));
+  return v;
+}
+
+template <int KC>
+__device__ __forceinline__ void load_rows3(const PointTable<KC> *__restrict__ t, const char *__restrict__ vbase, uint32_t pitch_bytes,
+                                           Rows &r) {
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    r.lo[d] = load_row(vbase, t->lower_row[d], pitch_bytes);
+    r.up[d] = load_row(vbase, t->upper_row[d], pitch_bytes);
+  }
+}
+
+// One grid point for the thread's two paths (LSV.cs:310-336).  `r` holds the rows of v_next this point interpolates between;
+// as soon as a decision has consumed its pair of rows the same registers are re-loaded with the rows that decision needs at
+// the warp's next grid point (record tn), so every load has most of a grid point's arithmetic to complete behind.
+template <int KP, int KC, bool FUSED>
+__device__ __forceinline__ void evaluate3(const PointTable<KC> *__restrict__ t, const PointTable<KC> *__restrict__ tn,
+                                          const char *__restrict__ vbase, uint32_t pitch_bytes, Rows &r, const double (&q0)[KP],
+                                          const double (&q1)[KP], double price0, double price1, double df, double &v0, double &v1) {
+  double best0 = 0.0, best1 = 0.0, adj0 = 0.0, adj1 = 0.0;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    if (FUSED) {
+      const DecisionF f = *reinterpret_cast<const DecisionF *>(&t->a[d]);
+      const double *c = t->c[d];
+      const double real0 = __fma_rn(r.up[d].x, f.upper_w, r.lo[d].x * f.lower_w);  // realised continuation value (LSV.cs:296-302)
+      const double real1 = __fma_rn(r.up[d].y, f.upper_w, r.lo[d].y * f.lower_w);
+      r.lo[d] = load_row(vbase, tn->lower_row[d], pitch_bytes);
+      r.up[d] = load_row(vbase, tn->upper_row[d], pitch_bytes);
+      double cont0 = q0[0] * c[0], cont1 = q1[0] * c[0];
+#pragma unroll
+      for (int k = 1; k < KP; ++k) {
+        cont0 = __fma_rn(q0[k], c[k], cont0);
+        cont1 = __fma_rn(q1[k], c[k], cont1);
+      }
+      const double pay0 = __fma_rn(price0, f.price_coef, f.offset), pay1 = __fma_rn(price1, f.price_coef, f.offset);
+      const double t0 = pay0 + cont0, t1 = pay1 + cont1;  // what the argmax is taken over (LSV.cs:317-327)
+      const double w0 = pay0 + real0, w1 = pay1 + real1;
+      if (d == 0 || t0 > best0) {
+        best0 = t0;
+        v0 = w0;
+      }
+      if (d == 0 || t1 > best1) {
+        best1 = t1;
+        v1 = w1;
+      }
+    } else {
+      evaluate_decision<KP>(d == 0, t->a[d], t->upper_w[d], t->c[d], r.lo[d], r.up[d], q0, q1, price0, price1, df, t->inv_cost, best0,
+                            best1, adj0, adj1);
+      r.lo[d] = load_row(vbase, tn->lower_row[d], pitch_bytes);
+      r.up[d] = load_row(vbase, tn->upper_row[d], pitch_bytes);
+    }
+  }
+  if (!FUSED) {
+    v0 = best0 + adj0;  // LSV.cs:333
+    v1 = best1 + adj1;
+  }
+}
+
+template <int KP, bool FUSED>
+__global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_sweep_kernel(BackwardStepArgs a) {
+  constexpr int KC = (KP + 1) & ~1;
+  constexpr int MB = KP <= 8 ? 1 : 2;  // 8-row blocks of the regression sums
+  constexpr int ACC = 8 * MB;          // width of a stored partial-sum row
+  using Table = PointTable<KC>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Table *s_tab = reinterpret_cast<Table *>(smem_raw);              // [kTabRing]
+  double *s_v = reinterpret_cast<double *>(s_tab + kTabRing);      // [2][kBlockG][kVPitch]
+  double *s_acc = s_v + 2 * kBlockG * kVPitch;                     // [2][kSweepWarps][kBlockG][ACC]
+
+  const int K = a.K;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = warp & (kSlots - 1), group = warp / kSlots;
+  const int64_t tile = blockIdx.y;
+  const int64_t n0 = tile * kSweepTilePaths + group * kGroupPaths + 2 * lane;
+  const bool valid0 = n0 < a.N;
+  // Threads beyond the last path work on a clamped (valid, even) column pair and never store; the odd column of a
+  // half-valid pair is the padding column of the row buffers, which holds finite values throughout (zero basis rows,
+  // zero terminal values).  Neither reaches the regression sums: the q_prev fragments below are zero beyond N.
+  const int64_t c0 = valid0 ? n0 : ((a.N - 1) & ~int64_t(1));
+  const int64_t c1 = min(c0 + 1, a.N - 1);
+
+  // this CTA's grid points
+  const int total_blocks = (a.G + kBlockG - 1) / kBlockG;
+  const int bbeg = blockIdx.x * a.subtiles_per_cta;
+  const int nblocks = min(bbeg + a.subtiles_per_cta, total_blocks) - bbeg;
+  if (nblocks <= 0) return;
+  const int gbeg = bbeg * kBlockG;
+  const int glimit = min(a.G, (bbeg + nblocks) * kBlockG) - gbeg;  // grid points of this CTA, addressed 0..glimit-1 below
+
+  const Table *tab = reinterpret_cast<const Table *>(a.point_tables) + gbeg;
+  auto stage = [&](int sub) {  // records [32 sub, 32 sub + 32) of this CTA's range into their half of the ring
+    const int first = sub * kTabSub;
+    const int count = min(kTabSub, glimit - first);
+    if (count <= 0) return;
+    const char *src = reinterpret_cast<const char *>(tab + first);
+    char *dst = reinterpret_cast<char *>(s_tab + (sub & 1) * kTabSub);
+    const int chunks = count * (int)(sizeof(Table) / 16);
+    for (int i = threadIdx.x; i < chunks; i += kSweepThreads) cp_async_16(dst + 16 * i, src + 16 * i);
+  };
+  stage(0);
+  stage(1);
+
+  double price0, price1;
+  if (a.spot) {
+    price0 = a.spot[c0];
+    price1 = a.spot[c1];
+  } else {
+    price0 = price1 = a.const_price;
+  }
+  // orthonormal basis row of this period for the thread's two paths (continuation value = q . c)
+  double q0[KP], q1[KP];
+#pragma unroll
+  for (int k = 0; k < KP; ++k) {
+    q0[k] = q1[k] = 0.0;
+    if (k < K && a.q_this) {
+      const double2 t = *reinterpret_cast<const double2 *>(a.q_this + (size_t)k * a.pitch + c0);
+      q0[k] = t.x;
+      q1[k] = t.y;
+    }
+  }
+  if (!a.q_this) q0[0] = q1[0] = 1.0;  // mean mode: continuation value = gamma[g][0]
+
+  // A operand of the regression GEMM for this warp's 16-path slice of the CTA: q_prev[k][slice], fragment layout of
+  // mma.m8n8k4 (row = lane / 4 -> k, col = lane % 4 -> path inside a chunk of 4).  Paths beyond N contribute zero.
+  const int row = lane >> 2, col = lane & 3;
+  double afrag[MB][4];
+#pragma unroll
+  for (int mb = 0; mb < MB; ++mb) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = mb * 8 + row;
+      const int64_t p = tile * kSweepTilePaths + 16 * warp + 4 * j + col;
+      double v = 0.0;
+      if (a.accumulate && k < K && p < a.N) v = a.q_prev ? a.q_prev[(size_t)k * a.pitch + p] : (k == 0 ? 1.0 : 0.0);
+      afrag[mb][j] = v;
+    }
+  }
+
+  const double df = a.settle_df;
+  const uint32_t pitch_bytes = (uint32_t)a.pitch * 8u;
+  // this thread's two columns of every v_next row; produced by a wide multiply-add so that it lives in an aligned register
+  // pair and row addresses are a single IMAD.WIDE each
+  const char *vbase = row_address(reinterpret_cast<const char *>(a.v_next), (uint32_t)c0, 8u);
+  // this warp's grid points are slot, slot + 4, ...: two per block.  Points past the end of the CTA's range are evaluated
+  // on the last record instead (and not stored), so the loop body is branch-free.
+  const int last = glimit - 1;
+  char *vout = reinterpret_cast<char *>(a.v_this + (size_t)gbeg * a.pitch + n0) + (uint64_t)slot * pitch_bytes;
+  double *my_v = s_v + (size_t)slot * kVPitch + group * kGroupPaths + 2 * lane;   // + buffer; second point kSlots rows further
+  const double *my_b = s_v + (size_t)row * kVPitch + 16 * warp + col;             // B fragments of this warp's slice
+  double *my_c = s_acc + (size_t)warp * kBlockG * ACC + (2 * col) * ACC + row;    // C fragment destination
+
+  auto combine = [&](int b) {  // partial sums of block b: the 8 warps' slices added in warp order
+    if (threadIdx.x < kBlockG * ACC) {
+      const int g8 = threadIdx.x / ACC, k = threadIdx.x - g8 * ACC;
+      const int g = b * kBlockG + g8;
+      if (g < glimit) {
+        const double *src = s_acc + (size_t)(b & 1) * kSweepWarps * kBlockG * ACC + g8 * ACC + k;
+        double sum = src[0];
+#pragma unroll
+        for (int w = 1; w < kSweepWarps; ++w) sum += src[(size_t)w * kBlockG * ACC];
+        a.partials[((size_t)tile * a.G + gbeg + g) * ACC + k] = sum;
+      }
+    }
+  };
+
+  cp_async_wait_all();
+  __syncthreads();
+
+  Rows rows;
+  load_rows3(s_tab + min(slot, last), vbase, pitch_bytes, rows);
+  for (int b = 0; b < nblocks; ++b) {
+    // this warp's two grid points of the block, and its first one of the next block (rows requested one point ahead)
+    const int gA = b * kBlockG + slot, gB = gA + kSlots, gA2 = gA + kBlockG;
+    const Table *tA = s_tab + (min(gA, last) & (kTabRing - 1));
+    const Table *tB = s_tab + (min(gB, last) & (kTabRing - 1));
+    const Table *tA2 = s_tab + (min(gA2, last) & (kTabRing - 1));
+    double vA0, vA1, vB0, vB1;
+#if LSMC_SWEEP_PF > 0
+    // the window's top row climbs about one row per grid point: ask L2 for the rows it reaches a few points from now
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(row_address(vbase, tA->ahead_row, pitch_bytes)));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(row_address(vbase, tB->ahead_row, pitch_bytes)));
+#endif
+    evaluate3<KP, KC, FUSED>(tA, tB, vbase, pitch_bytes, rows, q0, q1, price0, price1, df, vA0, vA1);
+    evaluate3<KP, KC, FUSED>(tB, tA2, vbase, pitch_bytes, rows, q0, q1, price0, price1, df, vB0, vB1);
+    if (valid0) {
+      if (gA <= last) *reinterpret_cast<double2 *>(vout) = make_double2(vA0, vA1);
+      if (gB <= last) *reinterpret_cast<double2 *>(vout + (uint64_t)kSlots * pitch_bytes) = make_double2(vB0, vB1);
+    }
+    vout += (uint64_t)kBlockG * pitch_bytes;
+    const int buf = b & 1;
+    if (a.accumulate) {
+      double *vt = my_v + buf * (kBlockG * kVPitch);
+      *reinterpret_cast<double2 *>(vt) = make_double2(vA0, vA1);
+      *reinterpret_cast<double2 *>(vt + kSlots * kVPitch) = make_double2(vB0, vB1);
+    }
+    // records of the next sub-tile must be visible one block before its first block, whose rows are requested in the
+    // last block of this sub-tile
+    if ((b & 3) == 2) cp_async_wait_all();
+    __syncthreads();
+    if ((b & 3) == 3) stage((b >> 2) + 2);  // every warp is done with the sub-tile that ends here: refill its half
+    if (a.accumulate) {
+      // C[k][g] = sum over the warp's 16 paths of q_prev[k][n] * V[g][n]; C fragment: row -> k, columns 2 col + {0,1} -> g
+      const double *vb = my_b + buf * (kBlockG * kVPitch);
+      double *dst = my_c + buf * (kSweepWarps * kBlockG * ACC);
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb) {
+        double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dmma_m8n8k4(acc0, acc1, afrag[mb][j], vb[4 * j]);
+        dst[mb * 8] = acc0;
+        dst[ACC + mb * 8] = acc1;
+      }
+      if (b > 0) combine(b - 1);  // complete since the barrier above
+    }
+  }
+  if (a.accumulate) {
+    __syncthreads();
+    combine(nblocks - 1);
+  }
+}
+
+template <int KP>
+void launch_sweep_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
+  if (a.fused_payoff) {
+    if (smem > 48 * 1024) cudaFuncSetAttribute(backward_sweep_kernel<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    backward_sweep_kernel<KP, true><<<grid, kSweepThreads, smem, stream>>>(a);
+  } else {
+    if (smem > 48 * 1024) cudaFuncSetAttribute(backward_sweep_kernel<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    backward_sweep_kernel<KP, false><<<grid, kSweepThreads, smem, stream>>>(a);
+  }
+}
+
+template <int KC>
+void launch_fold_for_kc(const FoldArgs &f, cudaStream_t stream) {
+  fold_tables_kernel<KC><<<(f.G * 3 + 127) / 128, 128, 0, stream>>>(f);
+}
+
+int coef_width(int KP) { return (KP + 1) & ~1; }
+
+}  // namespace
+
+size_t point_table_bytes(int K) {
+  switch (coef_width(padded_basis(K))) {
+    case 2: return sizeof(PointTable<2>);
+    case 4: return sizeof(PointTable<4>);
+    case 6: return sizeof(PointTable<6>);
+    case 8: return sizeof(PointTable<8>);
+    case 12: return sizeof(PointTable<12>);
+    default: return sizeof(PointTable<16>);
+  }
+}
+
+size_t backward_sweep_smem_bytes(int K) {
+  const int KP = padded_basis(K);
+  const int ACC = KP <= 8 ? 8 : 16;
+  return point_table_bytes(K) * kTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kSweepWarps * kBlockG * ACC);
+}
+
+void launch_fold_tables(const FoldArgs &f, cudaStream_t stream) {
+  switch (coef_width(padded_basis(f.K))) {
+    case 2: launch_fold_for_kc<2>(f, stream); break;
+    case 4: launch_fold_for_kc<4>(f, stream); break;
+    case 6: launch_fold_for_kc<6>(f, stream); break;
+    case 8: launch_fold_for_kc<8>(f, stream); break;
+    case 12: launch_fold_for_kc<12>(f, stream); break;
+    default: launch_fold_for_kc<16>(f, stream); break;
+  }
+}
+
+void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream) {
+  const dim3 grid(gsplit, (unsigned)num_tiles);
+  const size_t smem = backward_sweep_smem_bytes(a.K);
+  switch (padded_basis(a.K)) {
+    case 1: launch_sweep_for_k<1>(a, grid, smem, stream); break;
+    case 2: launch_sweep_for_k<2>(a, grid, smem, stream); break;
+    case 3: launch_sweep_for_k<3>(a, grid, smem, stream); break;
+    case 4: launch_sweep_for_k<4>(a, grid, smem, stream); break;
+    case 5: launch_sweep_for_k<5>(a, grid, smem, stream); break;
+    case 6: launch_sweep_for_k<6>(a, grid, smem, stream); break;
+    case 7: launch_sweep_for_k<7>(a, grid, smem, stream); break;
+    case 8: launch_sweep_for_k<8>(a, grid, smem, stream); break;
+    case 12: launch_sweep_for_k<12>(a, grid, smem, stream); break;
+    default: launch_sweep_for_k<16>(a, grid, smem, stream); break;
+  }
+}
+
+}  // namespace lsmc

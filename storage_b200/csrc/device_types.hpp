@@ -12,6 +12,7 @@ constexpr int kTilePaths = kThreads * kPathsPerThread;
 constexpr int kWarps = kThreads / 32;
 constexpr int kAccK = 8;                 // regression partial sums are stored padded to 8 (or 16) per grid point
 constexpr int kMaxGridTile = 16;         // inventory-grid points per CTA in the backward kernel
+constexpr int kSweepTilePaths = 128;     // paths per CTA of the three-decision sweep kernel (backward_sweep.cu)
 
 // Device copy of host_model.hpp's DecisionEntry (same layout).
 struct DevDecision {
@@ -47,12 +48,14 @@ struct BackwardStepArgs {
   const double *q_prev; // [K][pitch] basis rows of period-1 for the regression sums (NULL with accumulate: mean mode)
   int accumulate;       // 0: no further regression (period 0)
   double *partials;     // [num_tiles][G][acc] per-tile sums of q_prev[k] * v_this[g]
-  int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring kernel)
+  int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring and sweep kernels)
+  const void *point_tables;  // sweep kernel: [G] per-grid-point records written by fold_tables_kernel
   // ring kernel only: rows of v_next needed by each group of 8 grid points, and the ring size in rows
   const int32_t *win_lo, *win_hi;
   int ring_rows;
   // terminal mode: v_this[g][n] = TerminalStorageNpv(spot[n], grid_this[g]) instead of the decision step
   int terminal_mode;
+  int fused_payoff;     // 1: fused-payoff arithmetic (backward_common.cuh point_fused); 0: the reference's operation order
   const double *grid_this;  // [G]
   double terminal[4];
 };

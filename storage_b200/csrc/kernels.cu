@@ -261,7 +261,11 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
   for (int i = threadIdx.x; i < K * K; i += blockDim.x) s_rinv[i] = dd{a.spec.rinv[2 * i], a.spec.rinv[2 * i + 1]};
   __syncthreads();
   const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= a.N) return;
+  if (n >= a.N) {  // padding columns of the rows stay zero: the backward kernels load them as the odd half of a double2
+    if (n < a.pitch)
+      for (int k = 0; k < K; ++k) a.q_out[(size_t)k * a.pitch + n] = 0.0;
+    return;
+  }
   double q[KP];
   eval_q<KP>(a.spec, s_pw, s_rinv, K, F, n, true, q);
 #pragma unroll
@@ -290,7 +294,9 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
 #endif
 // DFIX: decision-table row width when it is the usual 3 (no extra decisions) so the table indexing folds at compile time;
 // 0 = run-time width.
-template <int KP, int DFIX>
+// FUSED (only with DFIX == 3): fused-payoff arithmetic of backward_common.cuh's point_fused instead of the reference's
+// operation order.
+template <int KP, int DFIX, bool FUSED>
 __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_step_kernel(BackwardStepArgs a) {
   constexpr int ACC = KP <= 8 ? 8 : 16;       // width of a stored partial-sum row
   constexpr int KC = (KP + 1) & ~1;           // coefficient row padded to an even length (16-byte rows)
@@ -370,7 +376,10 @@ __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_ste
         const int g = i / D;
         if (i - g * D < a.num_decisions[g0 + g]) {
           const DevDecision e = a.decisions[(size_t)g0 * D + i];
-          s_a[i] = DecisionA{-e.volume, -e.consumed, e.cost_npv, e.lower_w};
+          if (FUSED)
+            s_a[i] = DecisionA{(-e.volume - e.consumed) * a.settle_df, -(e.cost_npv + a.inventory_cost[g0 + g]), e.lower_w, e.upper_w};
+          else
+            s_a[i] = DecisionA{-e.volume, -e.consumed, e.cost_npv, e.lower_w};
           s_b[i] = DecisionR{e.upper_w, (uint32_t)e.lower * (uint32_t)a.pitch, (uint32_t)e.upper * (uint32_t)a.pitch};
           fold_coefficients<KC>(e, a.gamma, K, s_coef + (size_t)i * KC);
         }
@@ -411,9 +420,17 @@ __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_ste
         }
 #endif
         if (second) load_rows(pb + 3, s_nd[g + 1], vbase, rows_b);
-        point<KP, KC>(pa, pb, pc, s_nd[g], s_inv_cost[g], rows_a, q0, q1, price0, price1, df, v0, v1);
+        if (FUSED)
+          point_fused<KP, KC>(reinterpret_cast<const DecisionF *>(pa), pc, s_nd[g], rows_a, q0, q1, price0, price1, v0, v1);
+        else
+          point<KP, KC>(pa, pb, pc, s_nd[g], s_inv_cost[g], rows_a, q0, q1, price0, price1, df, v0, v1);
         if (g + 2 < gcount) load_rows(pb + 6, s_nd[g + 2], vbase, rows_a);
-        if (second) point<KP, KC>(pa + 3, pb + 3, pc + 3 * KC, s_nd[g + 1], s_inv_cost[g + 1], rows_b, q0, q1, price0, price1, df, w0, w1);
+        if (second) {
+          if (FUSED)
+            point_fused<KP, KC>(reinterpret_cast<const DecisionF *>(pa + 3), pc + 3 * KC, s_nd[g + 1], rows_b, q0, q1, price0, price1, w0, w1);
+          else
+            point<KP, KC>(pa + 3, pb + 3, pc + 3 * KC, s_nd[g + 1], s_inv_cost[g + 1], rows_b, q0, q1, price0, price1, df, w0, w1);
+        }
       } else if (a.terminal_mode) {
         // V_T[g][n] = TerminalStorageNpv(S_T[n], grid_T[g]) (LSV.cs:121-131)
         const double inv = a.grid_this[g0 + g], inv2 = second ? a.grid_this[g0 + g + 1] : 0.0;
@@ -831,17 +848,23 @@ void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t sme
       break;
     case 2:
       if (static_cast<const BackwardStepArgs *>(args)->D == 3) {
-        if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        backward_step_kernel<KP, 3><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
+        const BackwardStepArgs &ba = *static_cast<const BackwardStepArgs *>(args);
+        if (ba.fused_payoff && !ba.terminal_mode) {
+          if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+          backward_step_kernel<KP, 3, true><<<grid, block, smem, stream>>>(ba);
+        } else {
+          if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+          backward_step_kernel<KP, 3, false><<<grid, block, smem, stream>>>(ba);
+        }
         break;
       }
-      if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       {
         static int carve = -2;
         if (carve == -2) { const char *e = getenv("LSMC_CARVEOUT"); carve = e ? atoi(e) : -1; }
-        if (carve >= 0) cudaFuncSetAttribute(backward_step_kernel<KP, 0>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        if (carve >= 0) cudaFuncSetAttribute(backward_step_kernel<KP, 0, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
       }
-      backward_step_kernel<KP, 0><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
+      backward_step_kernel<KP, 0, false><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
       break;
     case 4:
       basis_kernel<KP><<<grid, block, 0, stream>>>(*static_cast<const BasisArgs *>(args));

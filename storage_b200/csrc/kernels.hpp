@@ -42,6 +42,20 @@ struct ReduceArgs {
   double *out;             // [G][K]
 };
 
+// Inputs of fold_tables_kernel (backward_sweep.cu): one record per grid point of the step with everything that does not
+// depend on the path.
+struct FoldArgs {
+  int G, Gn, K;  // grid points of this period and of the next, basis functions
+  int64_t pitch;
+  const DevDecision *decisions;  // [G][3]
+  const int32_t *num_decisions;  // [G]
+  const double *inventory_cost;  // [G]
+  const double *gamma;           // [Gn][K]
+  double settle_df;
+  int fused_payoff;
+  void *out;                     // [G] records of point_table_bytes(K) each
+};
+
 int padded_basis(int K);
 inline int acc_width(int K) { return padded_basis(K) <= 8 ? 8 : 16; }
 size_t backward_smem_bytes(int KP, int D);
@@ -54,6 +68,12 @@ void launch_basis(const BasisArgs &a, cudaStream_t stream);
 // TMA-staged variant (backward_ring.cu); gsplit CTAs per path tile, each sweeping a.subtiles_per_cta groups of 8 grid points
 size_t backward_ring_smem_bytes(int KP, int D, int ring_rows);
 void launch_backward_ring(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
+// Three-decision sweep kernel (backward_sweep.cu): gsplit CTAs per 128-path tile, each sweeping a.subtiles_per_cta blocks of 8
+// grid points; partial sums are laid out [tile of 128 paths][G][acc].
+size_t point_table_bytes(int K);
+size_t backward_sweep_smem_bytes(int K);
+void launch_fold_tables(const FoldArgs &f, cudaStream_t stream);
+void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream);
 // out[i] = sum over ranks r of all[r][i] (rank order); mean_mode: component 0 of every K-vector divided by total_paths, rest 0

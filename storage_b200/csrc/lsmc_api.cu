@@ -97,6 +97,7 @@ struct lsmc_handle {
   DeviceBuffer<double> v_a, v_b, grids, gamma, rinv, partials, gram_partials, inv_cost, pv, final_inv, step_sums, step_totals,
       block_sums, gather_buf, qbuf[2], ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
   DeviceBuffer<DevDecision> decisions;
+  DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag, win_lo, win_hi;
   std::vector<size_t> window_offset;  // per period: first group in win_lo / win_hi
   std::vector<int> ring_rows;         // per period: ring size the TMA-staged kernel needs (0: use the direct-load kernel)
@@ -482,6 +483,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   const int64_t num_tiles = (N + kTilePaths - 1) / kTilePaths;
   int sm_count = 148;
   cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device);
+  static const bool use_sweep = [] { const char *e = std::getenv("LSMC_SWEEP"); return !(e && e[0] == '0'); }();  // test hook
   auto q_buffer = [&](int period) { return h->qbuf[period & 1].ptr; };
   auto has_basis = [&](int period) { return period >= first_reg && period < P; };
   auto launch_basis_for = [&](int period) {
@@ -511,6 +513,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.v_next = v_next;
     a.v_this = v_this;
     a.terminal_mode = terminal ? 1 : 0;
+    a.fused_payoff = (h->flags & LSMC_REFERENCE_OPERATION_ORDER) ? 0 : 1;
     if (terminal) {
       a.grid_this = h->grids.ptr + (size_t)p * Gmax;
       a.spot = h->sims[0].spot + (size_t)(p - h->first_sim) * N;
@@ -535,26 +538,48 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.partials = h->partials.ptr;
     // split the inventory grid over several CTAs only when there are too few path tiles to fill the GPU
     const bool ring = !terminal && h->ring_rows[p] > 0;
-    const int sub_size = ring ? 8 : kMaxGridTile;
+    const bool sweep = !terminal && !ring && D == 3 && use_sweep;
+    const int sub_size = (ring || sweep) ? 8 : kMaxGridTile;
     const int subtiles = (a.G + sub_size - 1) / sub_size;
-    const int64_t slots = (int64_t)sm_count * (ring ? 2 : 4);
-    int gsplit = (int)std::min<int64_t>(subtiles, std::max<int64_t>(1, (4 * slots + num_tiles - 1) / num_tiles));
+    const int64_t tiles = sweep ? (N + kSweepTilePaths - 1) / kSweepTilePaths : num_tiles;
+    const int64_t slots = (int64_t)sm_count * ((ring || sweep) ? 2 : 4);
+    int gsplit = (int)std::min<int64_t>(subtiles, std::max<int64_t>(1, (4 * slots + tiles - 1) / tiles));
     if (const char *forced = std::getenv("LSMC_GSPLIT")) gsplit = std::max(1, std::min(subtiles, std::atoi(forced)));  // test hook
     a.subtiles_per_cta = (subtiles + gsplit - 1) / gsplit;
     gsplit = (subtiles + a.subtiles_per_cta - 1) / a.subtiles_per_cta;
+    if (sweep) {
+      // per-grid-point records: payoffs, weights, row offsets and the folded regression coefficients (needs this step's gamma)
+      FoldArgs f{};
+      f.G = a.G;
+      f.Gn = a.Gn;
+      f.K = K;
+      f.pitch = h->pitch;
+      f.decisions = a.decisions;
+      f.num_decisions = a.num_decisions;
+      f.inventory_cost = a.inventory_cost;
+      f.gamma = a.gamma;
+      f.settle_df = a.settle_df;
+      f.fused_payoff = a.fused_payoff;
+      f.out = h->point_tables.ptr;
+      launch_fold_tables(f, st);
+      launches++;
+      a.point_tables = h->point_tables.ptr;
+    }
     if (!terminal) cudaEventRecord(step_events[2 * p], st);
     if (ring) {
       a.win_lo = h->win_lo.ptr + h->window_offset[p];
       a.win_hi = h->win_hi.ptr + h->window_offset[p];
       a.ring_rows = h->ring_rows[p];
       launch_backward_ring(a, gsplit, num_tiles, st);
+    } else if (sweep) {
+      launch_backward_sweep(a, gsplit, tiles, st);
     } else {
       launch_backward_step(a, gsplit, num_tiles, st);
     }
     if (!terminal) cudaEventRecord(step_events[2 * p + 1], st);
     launches++;
-    dbg(ring ? "backward_ring_kernel" : "backward_step_kernel", p);
-    return (int)num_tiles;
+    dbg(ring ? "backward_ring_kernel" : sweep ? "backward_sweep_kernel" : "backward_step_kernel", p);
+    return (int)tiles;
   };
   auto reduce_gamma = [&](int p, int G_next, int num_chunks) {
     // regression coefficients of V_{p+1} on period p's basis (LSV.cs:199-212) from the partial sums the kernel that
@@ -799,8 +824,9 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     h->gamma.allocate((size_t)h->P * h->Gmax * h->K);
     h->rinv.allocate((size_t)h->P * h->K * h->K * 2);
     CUDA_OK(cudaMemset(h->rinv.ptr, 0, h->rinv.count * sizeof(double)));
-    const int64_t num_tiles = (h->N + kTilePaths - 1) / kTilePaths;
+    const int64_t num_tiles = (h->N + kSweepTilePaths - 1) / kSweepTilePaths;  // the finer of the two kernels' tilings
     h->partials.allocate((size_t)num_tiles * h->Gmax * h->acc_k);
+    h->point_tables.allocate((size_t)h->Gmax * point_table_bytes(h->K) / sizeof(double));
     h->qbuf[0].allocate((size_t)h->K * h->pitch);
     h->qbuf[1].allocate((size_t)h->K * h->pitch);
     h->pv.allocate(h->N);

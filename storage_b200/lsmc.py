@@ -581,8 +581,12 @@ class LsmcStorageValuation:
         self._logger = logger
         self._device = device
 
-    def Calculate(self, lsmcParams, keep_decisions=False):
-        """LsmcStorageValuation.Calculate (LSV.cs:57-657)."""
+    def Calculate(self, lsmcParams, keep_decisions=False, reference_operation_order=False):
+        """LsmcStorageValuation.Calculate (LSV.cs:57-657).
+
+        keep_decisions and reference_operation_order have no reference counterpart: the first keeps the argmax index panel,
+        the second evaluates each decision's cash flow in the reference's own sequence of roundings (LSV.cs:317-336) instead
+        of the default fused form (include/lsmc_b200.h LSMC_REFERENCE_OPERATION_ORDER)."""
         p = lsmcParams
         notify = p.OnProgressUpdate
         if p.Inventory < 0:  # LSV.cs:64-65
@@ -610,7 +614,8 @@ class LsmcStorageValuation:
         else:
             model, num_sims = spec[1], spec[2]
             num_factors = model.NumFactors
-        flat = FlatProblem(p, num_sims, num_factors, extra_flags=_abi.LSMC_RETURN_DECISION_INDEX if keep_decisions else 0)
+        flat = FlatProblem(p, num_sims, num_factors, extra_flags=(_abi.LSMC_RETURN_DECISION_INDEX if keep_decisions else 0)
+                           | (_abi.LSMC_REFERENCE_OPERATION_ORDER if reference_operation_order else 0))
         if spec[0] == "panels":  # CheckSpotSim (LVP.cs:219-231): host-side, before any device call
             for name, sims in (("regressionSpotSim", reg), ("valuationSpotSim", val)):
                 have = set(sims.SimulatedPeriods)

@@ -172,5 +172,6 @@ def three_factor_ratchets(num_sims=2000, num_days=60, seed=11, val_offset=-1, in
     return _finish(storage, val_date, inventory, model, basis, num_sims, seed, grid_points, **kw)
 
 
-def run_gpu(case, keep_decisions=True, device=0):
-    return LsmcStorageValuation(device=device).Calculate(case.params, keep_decisions=keep_decisions)
+def run_gpu(case, keep_decisions=True, device=0, reference_operation_order=False):
+    return LsmcStorageValuation(device=device).Calculate(case.params, keep_decisions=keep_decisions,
+                                                        reference_operation_order=reference_operation_order)

@@ -26,9 +26,16 @@ def material_mismatches(gpu, ref):
 
 
 def check_case(case, rel=REL):
+    """Both arithmetic forms of the backward kernel (default fused payoff, and the reference's operation order) against the oracle."""
     case.params.SimulationDataReturned = SimulationDataReturned.All
-    gpu = cases.run_gpu(case)
     ref = oracle.lsmc_calculate(case.flat, case.reg_spot, case.reg_factors, case.val_spot, case.val_factors, mode=1)
+    for reference_order in (False, True):
+        gpu = cases.run_gpu(case, reference_operation_order=reference_order)
+        compare_with_oracle(case, gpu, ref, rel)
+    return gpu, ref
+
+
+def compare_with_oracle(case, gpu, ref, rel):
     raw, material = material_mismatches(gpu, ref)
     assert material == 0, f"{material} material decision mismatches ({raw} raw index flips)"
     assert gpu.Npv == pytest.approx(ref.npv, rel=rel)
