@@ -85,8 +85,9 @@ __global__ void fold_tables_kernel(FoldArgs f) {
   else
     t->a[d] = DecisionA{-e.volume, -e.consumed, e.cost_npv, e.lower_w};
   t->upper_w[d] = e.upper_w;
-  t->lower_row[d] = (uint32_t)e.lower;
-  t->upper_row[d] = (uint32_t)e.upper;
+  // direct-load kernel: row indices; row-ring kernel: byte offsets of the rows' slots in the shared-memory ring
+  t->lower_row[d] = f.ring_rows > 0 ? (uint32_t)(e.lower % f.ring_rows) * (uint32_t)(kSweepTilePaths * 8) : (uint32_t)e.lower;
+  t->upper_row[d] = f.ring_rows > 0 ? (uint32_t)(e.upper % f.ring_rows) * (uint32_t)(kSweepTilePaths * 8) : (uint32_t)e.upper;
   fold_coefficients<KC>(e, f.gamma, f.K, t->c[d]);
 }
 
@@ -99,7 +100,7 @@ __device__ __forceinline__ const char *row_address(const char *base, uint32_t ro
 // 16-byte load of this thread's two columns of row `row` (v_next is read-only for the whole launch)
 __device__ __forceinline__ double2 load_row(const char *base, uint32_t row, uint32_t pitch_bytes) {
   double2 v;
-  asm("{\n\t.reg .u64 p;\n\tmad.wide.u32 p, %2, %3, %4;\n\tld.global.v2.f64 {%0, %1}, [p];\n\t}"
+  asm volatile("{\n\t.reg .u64 p;\n\tmad.wide.u32 p, %2, %3, %4;\n\tld.global.v2.f64 {%0, %1}, [p];\n\t}"
       : "=d"(v.x), "=d"(v.y)
       : "r"(row), "r"(pitch_bytes), "l"(base));
   return v;
@@ -325,6 +326,266 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Row-ring variant.  Same work layout, but the rows of v_next are not loaded by the evaluating threads: the window of rows
+// that a block of 8 grid points reads ([lo, hi], SweepBlock) lives in a shared-memory ring of R rows x 128 paths, and while
+// block b is evaluated the CTA copies the rows that block b+1 adds with cp.async (no registers held, one barrier per block
+// — the one the regression GEMM needs anyway) and asks L2 for the rows of block b+3.  Every row comes from HBM/L2 once per
+// CTA; the evaluation reads rows with conflict-free LDS.128 at offsets the fold kernel precomputed.  The host uses this
+// variant when the windows slide upwards and fit (lsmc_api.cu), otherwise the direct-load kernel above.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int kRowBytes = kSweepTilePaths * 8;
+constexpr int kRingTabSub = 16, kRingTabRing = 2 * kRingTabSub;
+
+template <int KP, int KC, bool FUSED>
+__device__ __forceinline__ void evaluate3_ring(const PointTable<KC> *__restrict__ t, const char *__restrict__ my_rows,
+                                               const double (&q0)[KP], const double (&q1)[KP], double price0, double price1, double df,
+                                               double &v0, double &v1) {
+  if (FUSED) {
+    // the three decisions' dot products advance together: six independent FMA chains instead of two
+    double cont0[3], cont1[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      cont0[d] = q0[0] * t->c[d][0];
+      cont1[d] = q1[0] * t->c[d][0];
+    }
+#pragma unroll
+    for (int k = 1; k < KP; ++k) {
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        cont0[d] = __fma_rn(q0[k], t->c[d][k], cont0[d]);
+        cont1[d] = __fma_rn(q1[k], t->c[d][k], cont1[d]);
+      }
+    }
+    double tt0[3], tt1[3], w0[3], w1[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const DecisionF f = *reinterpret_cast<const DecisionF *>(&t->a[d]);
+      const double2 lo = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d]);
+      const double2 up = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
+      const double pay0 = __fma_rn(price0, f.price_coef, f.offset), pay1 = __fma_rn(price1, f.price_coef, f.offset);
+      tt0[d] = pay0 + cont0[d];  // what the argmax is taken over (LSV.cs:317-327)
+      tt1[d] = pay1 + cont1[d];
+      w0[d] = pay0 + __fma_rn(up.x, f.upper_w, lo.x * f.lower_w);  // payoff + realised continuation (LSV.cs:296-302)
+      w1[d] = pay1 + __fma_rn(up.y, f.upper_w, lo.y * f.lower_w);
+    }
+    double best0 = tt0[0], best1 = tt1[0];
+    v0 = w0[0];
+    v1 = w1[0];
+#pragma unroll
+    for (int d = 1; d < 3; ++d) {  // first maximum wins (SH.cs:206-221)
+      if (tt0[d] > best0) {
+        best0 = tt0[d];
+        v0 = w0[d];
+      }
+      if (tt1[d] > best1) {
+        best1 = tt1[d];
+        v1 = w1[d];
+      }
+    }
+  } else {
+    double best0 = 0.0, best1 = 0.0, adj0 = 0.0, adj1 = 0.0;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const double2 lo = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d]);
+      const double2 up = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
+      evaluate_decision<KP>(d == 0, t->a[d], t->upper_w[d], t->c[d], lo, up, q0, q1, price0, price1, df, t->inv_cost, best0, best1, adj0,
+                            adj1);
+    }
+    v0 = best0 + adj0;  // LSV.cs:333
+    v1 = best1 + adj1;
+  }
+}
+
+template <int KP, bool FUSED>
+__global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_sweep_ring_kernel(BackwardStepArgs a) {
+  constexpr int KC = (KP + 1) & ~1;
+  constexpr int MB = KP <= 8 ? 1 : 2;
+  constexpr int ACC = 8 * MB;
+  using Table = PointTable<KC>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  Table *s_tab = reinterpret_cast<Table *>(smem_raw);                        // [kRingTabRing]
+  double *s_v = reinterpret_cast<double *>(s_tab + kRingTabRing);            // [2][kBlockG][kVPitch]
+  double *s_acc = s_v + 2 * kBlockG * kVPitch;                               // [2][kSweepWarps][kBlockG][ACC]
+  char *s_rows = reinterpret_cast<char *>(s_acc + 2 * kSweepWarps * kBlockG * ACC);  // [R][kRowBytes]
+  const int R = a.ring_rows;
+  SweepBlock *s_blk = reinterpret_cast<SweepBlock *>(s_rows + (size_t)R * kRowBytes);  // [a.subtiles_per_cta]
+
+  const int K = a.K;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = warp & (kSlots - 1), group = warp / kSlots;
+  const int64_t tile = blockIdx.y;
+  const int64_t n0 = tile * kSweepTilePaths + group * kGroupPaths + 2 * lane;
+  const bool valid0 = n0 < a.N;
+  // Columns beyond the last path are padding of the row buffers: zero in the basis rows and in the terminal values, hence
+  // finite in every row; threads that own them compute on them but never store, and the q_prev fragments are zero there.
+  const int64_t c0 = valid0 ? n0 : ((a.N - 1) & ~int64_t(1));
+  const int64_t c1 = min(c0 + 1, a.N - 1);
+
+  const int total_blocks = (a.G + kBlockG - 1) / kBlockG;
+  const int bbeg = blockIdx.x * a.subtiles_per_cta;
+  const int nblocks = min(bbeg + a.subtiles_per_cta, total_blocks) - bbeg;
+  if (nblocks <= 0) return;
+  const int gbeg = bbeg * kBlockG;
+  const int glimit = min(a.G, (bbeg + nblocks) * kBlockG) - gbeg;
+
+  const Table *tab = reinterpret_cast<const Table *>(a.point_tables) + gbeg;
+  auto stage = [&](int sub) {
+    const int first = sub * kRingTabSub;
+    const int count = min(kRingTabSub, glimit - first);
+    if (count <= 0) return;
+    const char *src = reinterpret_cast<const char *>(tab + first);
+    char *dst = reinterpret_cast<char *>(s_tab + (sub & 1) * kRingTabSub);
+    const int chunks = count * (int)(sizeof(Table) / 16);
+    for (int i = threadIdx.x; i < chunks; i += kSweepThreads) cp_async_16(dst + 16 * i, src + 16 * i);
+  };
+  // rows [first_row, first_row + count) of this tile's 128 columns into ring slots first_slot.. (mod R): one warp per row,
+  // two 16-byte pieces per lane
+  const uint32_t pitch_bytes = (uint32_t)a.pitch * 8u;
+  const char *tile_rows = reinterpret_cast<const char *>(a.v_next + tile * kSweepTilePaths) + lane * 16;
+  char *ring_dst = s_rows + lane * 16;
+  auto fetch_rows = [&](int first_row, int first_slot, int count) {
+    for (int j = warp; j < count; j += kSweepWarps) {
+      int s = first_slot + j;
+      if (s >= R) s -= R;
+      const char *src = row_address(tile_rows, (uint32_t)(first_row + j), pitch_bytes);
+      char *dst = ring_dst + s * kRowBytes;
+      cp_async_16(dst, src);
+      cp_async_16(dst + 512, src + 512);
+    }
+  };
+  auto request_rows = [&](int first_row, int count) {  // into L2 only: one 128-byte line per lane, lanes 0..7
+    if (lane < 8)
+      for (int j = warp; j < count; j += kSweepWarps)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(row_address(tile_rows, (uint32_t)(first_row + j), pitch_bytes) + lane * 112));
+  };
+
+  const SweepBlock *blk = a.sweep_blocks + bbeg;
+  stage(0);
+  {
+    const SweepBlock w = blk[0];
+    fetch_rows(w.lo, w.lo_slot, w.hi - w.lo + 1);
+    if (nblocks > 1) request_rows(w.hi + 1, blk[1].hi - w.hi);
+    if (nblocks > 2) request_rows(blk[1].hi + 1, blk[2].hi - blk[1].hi);
+  }
+  for (int i = threadIdx.x; i < nblocks; i += kSweepThreads) s_blk[i] = blk[i];
+
+  double price0, price1;
+  if (a.spot) {
+    price0 = a.spot[c0];
+    price1 = a.spot[c1];
+  } else {
+    price0 = price1 = a.const_price;
+  }
+  double q0[KP], q1[KP];
+#pragma unroll
+  for (int k = 0; k < KP; ++k) {
+    q0[k] = q1[k] = 0.0;
+    if (k < K && a.q_this) {
+      const double2 t = *reinterpret_cast<const double2 *>(a.q_this + (size_t)k * a.pitch + c0);
+      q0[k] = t.x;
+      q1[k] = t.y;
+    }
+  }
+  if (!a.q_this) q0[0] = q1[0] = 1.0;  // mean mode: continuation value = gamma[g][0]
+
+  const int row = lane >> 2, col = lane & 3;
+  double afrag[MB][4];
+#pragma unroll
+  for (int mb = 0; mb < MB; ++mb) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = mb * 8 + row;
+      const int64_t p = tile * kSweepTilePaths + 16 * warp + 4 * j + col;
+      double v = 0.0;
+      if (a.accumulate && k < K && p < a.N) v = a.q_prev ? a.q_prev[(size_t)k * a.pitch + p] : (k == 0 ? 1.0 : 0.0);
+      afrag[mb][j] = v;
+    }
+  }
+
+  const double df = a.settle_df;
+  const int last = glimit - 1;
+  char *vout = reinterpret_cast<char *>(a.v_this + (size_t)gbeg * a.pitch + n0) + (uint64_t)slot * pitch_bytes;
+  const char *my_rows = s_rows + group * (kGroupPaths * 8) + lane * 16;            // this thread's two columns of every ring row
+  double *my_v = s_v + (size_t)slot * kVPitch + group * kGroupPaths + 2 * lane;
+  const double *my_b = s_v + (size_t)row * kVPitch + 16 * warp + col;
+  double *my_c = s_acc + (size_t)warp * kBlockG * ACC + (2 * col) * ACC + row;
+
+  auto combine = [&](int b) {
+    if (threadIdx.x < kBlockG * ACC) {
+      const int g8 = threadIdx.x / ACC, k = threadIdx.x - g8 * ACC;
+      const int g = b * kBlockG + g8;
+      if (g < glimit) {
+        const double *src = s_acc + (size_t)(b & 1) * kSweepWarps * kBlockG * ACC + g8 * ACC + k;
+        double sum = src[0];
+#pragma unroll
+        for (int w = 1; w < kSweepWarps; ++w) sum += src[(size_t)w * kBlockG * ACC];
+        a.partials[((size_t)tile * a.G + gbeg + g) * ACC + k] = sum;
+      }
+    }
+  };
+
+  cp_async_wait_all();
+  __syncthreads();
+
+  for (int b = 0; b < nblocks; ++b) {
+    // every warp has finished block b-1: its table half and the ring slots below this block's window are free
+    if ((b & 1) == 0) stage((b >> 1) + 1);
+    if (b + 1 < nblocks) {
+      const SweepBlock cur = s_blk[b], nxt = s_blk[b + 1];
+      fetch_rows(cur.hi + 1, cur.hi_slot + 1, nxt.hi - cur.hi);
+      if (b + 3 < nblocks) request_rows(s_blk[b + 2].hi + 1, s_blk[b + 3].hi - s_blk[b + 2].hi);
+    }
+    const int gA = b * kBlockG + slot, gB = gA + kSlots;
+    const Table *tA = s_tab + (min(gA, last) & (kRingTabRing - 1));
+    const Table *tB = s_tab + (min(gB, last) & (kRingTabRing - 1));
+    double vA0, vA1, vB0, vB1;
+    evaluate3_ring<KP, KC, FUSED>(tA, my_rows, q0, q1, price0, price1, df, vA0, vA1);
+    evaluate3_ring<KP, KC, FUSED>(tB, my_rows, q0, q1, price0, price1, df, vB0, vB1);
+    if (valid0) {
+      if (gA <= last) *reinterpret_cast<double2 *>(vout) = make_double2(vA0, vA1);
+      if (gB <= last) *reinterpret_cast<double2 *>(vout + (uint64_t)kSlots * pitch_bytes) = make_double2(vB0, vB1);
+    }
+    vout += (uint64_t)kBlockG * pitch_bytes;
+    const int buf = b & 1;
+    if (a.accumulate) {
+      double *vt = my_v + buf * (kBlockG * kVPitch);
+      *reinterpret_cast<double2 *>(vt) = make_double2(vA0, vA1);
+      *reinterpret_cast<double2 *>(vt + kSlots * kVPitch) = make_double2(vB0, vB1);
+    }
+    cp_async_wait_all();  // this thread's share of the next block's rows (and table records) has landed ...
+    __syncthreads();      // ... and so has everybody else's
+    if (a.accumulate) {
+      const double *vb = my_b + buf * (kBlockG * kVPitch);
+      double *dst = my_c + buf * (kSweepWarps * kBlockG * ACC);
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb) {
+        double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dmma_m8n8k4(acc0, acc1, afrag[mb][j], vb[4 * j]);
+        dst[mb * 8] = acc0;
+        dst[ACC + mb * 8] = acc1;
+      }
+      if (b > 0) combine(b - 1);
+    }
+  }
+  if (a.accumulate) {
+    __syncthreads();
+    combine(nblocks - 1);
+  }
+}
+
+template <int KP>
+void launch_sweep_ring_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
+  if (a.fused_payoff) {
+    cudaFuncSetAttribute(backward_sweep_ring_kernel<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    backward_sweep_ring_kernel<KP, true><<<grid, kSweepThreads, smem, stream>>>(a);
+  } else {
+    cudaFuncSetAttribute(backward_sweep_ring_kernel<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    backward_sweep_ring_kernel<KP, false><<<grid, kSweepThreads, smem, stream>>>(a);
+  }
+}
+
 template <int KP>
 void launch_sweep_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
   if (a.fused_payoff) {
@@ -362,6 +623,13 @@ size_t backward_sweep_smem_bytes(int K) {
   return point_table_bytes(K) * kTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kSweepWarps * kBlockG * ACC);
 }
 
+size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta) {
+  const int KP = padded_basis(K);
+  const int ACC = KP <= 8 ? 8 : 16;
+  return point_table_bytes(K) * kRingTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kSweepWarps * kBlockG * ACC) +
+         (size_t)ring_rows * kRowBytes + (size_t)blocks_per_cta * sizeof(SweepBlock);
+}
+
 void launch_fold_tables(const FoldArgs &f, cudaStream_t stream) {
   switch (coef_width(padded_basis(f.K))) {
     case 2: launch_fold_for_kc<2>(f, stream); break;
@@ -375,6 +643,22 @@ void launch_fold_tables(const FoldArgs &f, cudaStream_t stream) {
 
 void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream) {
   const dim3 grid(gsplit, (unsigned)num_tiles);
+  if (a.ring_rows > 0) {
+    const size_t smem = backward_sweep_ring_smem_bytes(a.K, a.ring_rows, a.subtiles_per_cta);
+    switch (padded_basis(a.K)) {
+      case 1: launch_sweep_ring_for_k<1>(a, grid, smem, stream); break;
+      case 2: launch_sweep_ring_for_k<2>(a, grid, smem, stream); break;
+      case 3: launch_sweep_ring_for_k<3>(a, grid, smem, stream); break;
+      case 4: launch_sweep_ring_for_k<4>(a, grid, smem, stream); break;
+      case 5: launch_sweep_ring_for_k<5>(a, grid, smem, stream); break;
+      case 6: launch_sweep_ring_for_k<6>(a, grid, smem, stream); break;
+      case 7: launch_sweep_ring_for_k<7>(a, grid, smem, stream); break;
+      case 8: launch_sweep_ring_for_k<8>(a, grid, smem, stream); break;
+      case 12: launch_sweep_ring_for_k<12>(a, grid, smem, stream); break;
+      default: launch_sweep_ring_for_k<16>(a, grid, smem, stream); break;
+    }
+    return;
+  }
   const size_t smem = backward_sweep_smem_bytes(a.K);
   switch (padded_basis(a.K)) {
     case 1: launch_sweep_for_k<1>(a, grid, smem, stream); break;

@@ -28,6 +28,12 @@ struct BasisSpec {
   int mean_mode;                         // 1: q = e_0 (current-period step: continuation value = sample mean)
 };
 
+// Window of v_next rows that a block of 8 grid points reads (all decisions), as the row-ring sweep kernel consumes it:
+// hi is a running maximum, so block b+1 adds exactly the rows (hi(b), hi(b+1)]; the slots are the rows modulo the ring size.
+struct SweepBlock {
+  int32_t lo, hi, lo_slot, hi_slot;
+};
+
 struct BackwardStepArgs {
   int64_t N;            // paths on this device
   int64_t pitch;        // row pitch of the V and Q buffers, in doubles
@@ -49,6 +55,7 @@ struct BackwardStepArgs {
   int accumulate;       // 0: no further regression (period 0)
   double *partials;     // [num_tiles][G][acc] per-tile sums of q_prev[k] * v_this[g]
   int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring and sweep kernels)
+  const SweepBlock *sweep_blocks;  // row-ring sweep kernel: [blocks of 8 grid points] of this period
   const void *point_tables;  // sweep kernel: [G] per-grid-point records written by fold_tables_kernel
   // ring kernel only: rows of v_next needed by each group of 8 grid points, and the ring size in rows
   const int32_t *win_lo, *win_hi;

@@ -53,6 +53,7 @@ struct FoldArgs {
   const double *gamma;           // [Gn][K]
   double settle_df;
   int fused_payoff;
+  int ring_rows;                 // > 0: row offsets are written as slots of a ring of this many rows (row-ring sweep kernel)
   void *out;                     // [G] records of point_table_bytes(K) each
 };
 
@@ -72,6 +73,7 @@ void launch_backward_ring(const BackwardStepArgs &a, int gsplit, int64_t num_til
 // grid points; partial sums are laid out [tile of 128 paths][G][acc].
 size_t point_table_bytes(int K);
 size_t backward_sweep_smem_bytes(int K);
+size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta);
 void launch_fold_tables(const FoldArgs &f, cudaStream_t stream);
 void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);

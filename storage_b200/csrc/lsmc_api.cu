@@ -101,6 +101,8 @@ struct lsmc_handle {
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag, win_lo, win_hi;
   std::vector<size_t> window_offset;  // per period: first group in win_lo / win_hi
   std::vector<int> ring_rows;         // per period: ring size the TMA-staged kernel needs (0: use the direct-load kernel)
+  std::vector<int> sweep_ring_rows;   // per period: ring size of the row-ring sweep kernel (0: direct-load sweep kernel)
+  DeviceBuffer<SweepBlock> sweep_blocks;  // [window_offset[p] + block] row windows of the row-ring sweep kernel
   DeviceBuffer<DevPeriodParams> period_params;
   DeviceBuffer<BasisSpec> gram_specs;
   DeviceBuffer<double> panels[7];  // inventory, volume, consumed, loss, net volume, pv, decision index
@@ -306,6 +308,8 @@ void build_device_tables(lsmc_handle *h) {
     const char *ring_env = std::getenv("LSMC_RING");
     const bool no_ring = !(ring_env && std::atoi(ring_env) != 0);
     std::vector<int32_t> lo_all, hi_all;
+    std::vector<SweepBlock> blocks_all;
+    h->sweep_ring_rows.assign(P, 0);
     h->window_offset.assign(P, 0);
     h->ring_rows.assign(P, 0);
     for (int p = 0; p < P; ++p) {
@@ -330,9 +334,30 @@ void build_device_tables(lsmc_handle *h) {
       h->ring_rows[p] = ok ? std::max(need, 2) : 0;
       lo_all.insert(lo_all.end(), lo.begin(), lo.end());
       hi_all.insert(hi_all.end(), hi.begin(), hi.end());
+      // Row-ring sweep kernel (backward_sweep.cu): while block j is evaluated the rows block j+1 adds are copied in, so
+      // the ring must hold [lo(j), hi(j+1)] with hi a running maximum; usable when lo never decreases and the ring fits
+      // beside the kernel's other shared-memory buffers with two CTAs per SM.
+      {
+        constexpr int kMaxSweepRing = 64;
+        const char *env = std::getenv("LSMC_SWEEP_RING");  // test hook: 0 forces the direct-load sweep kernel
+        bool sweep_ok = !(env && env[0] == '0');
+        std::vector<int32_t> hic(hi);
+        for (int j = 1; j < groups; ++j) hic[j] = std::max(hic[j], hic[j - 1]);
+        int sweep_need = 0;
+        for (int j = 0; j < groups; ++j) {
+          if (j + 1 < groups && lo[j + 1] < lo[j]) sweep_ok = false;
+          sweep_need = std::max(sweep_need, hic[std::min(j + 1, groups - 1)] - lo[j] + 1);
+        }
+        if (sweep_need > kMaxSweepRing) sweep_ok = false;
+        const int R = sweep_ok ? std::max(sweep_need, 2) : 0;
+        h->sweep_ring_rows[p] = R;
+        for (int j = 0; j < groups; ++j)
+          blocks_all.push_back(SweepBlock{lo[j], hic[j], R ? lo[j] % R : 0, R ? hic[j] % R : 0});
+      }
     }
     h->win_lo.upload(lo_all);
     h->win_hi.upload(hi_all);
+    h->sweep_blocks.upload(blocks_all);
   }
 
   std::vector<double> grids((size_t)(P + 1) * Gmax, 0.0);
@@ -560,10 +585,13 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       f.gamma = a.gamma;
       f.settle_df = a.settle_df;
       f.fused_payoff = a.fused_payoff;
+      f.ring_rows = h->sweep_ring_rows[p];
       f.out = h->point_tables.ptr;
       launch_fold_tables(f, st);
       launches++;
       a.point_tables = h->point_tables.ptr;
+      a.ring_rows = h->sweep_ring_rows[p];
+      a.sweep_blocks = h->sweep_blocks.ptr + h->window_offset[p];
     }
     if (!terminal) cudaEventRecord(step_events[2 * p], st);
     if (ring) {
@@ -821,6 +849,9 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     CUDA_OK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->v_a.allocate((size_t)h->Gmax * h->pitch);
     h->v_b.allocate((size_t)h->Gmax * h->pitch);
+    // the padding columns [N, pitch) of the value rows are read (never written) by the sweep kernels: keep them finite
+    CUDA_OK(cudaMemset(h->v_a.ptr, 0, h->v_a.count * sizeof(double)));
+    CUDA_OK(cudaMemset(h->v_b.ptr, 0, h->v_b.count * sizeof(double)));
     h->gamma.allocate((size_t)h->P * h->Gmax * h->K);
     h->rinv.allocate((size_t)h->P * h->K * h->K * 2);
     CUDA_OK(cudaMemset(h->rinv.ptr, 0, h->rinv.count * sizeof(double)));
