@@ -327,100 +327,109 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// Row-ring variant.  Same work layout, but the rows of v_next are not loaded by the evaluating threads: the window of rows
-// that a block of 8 grid points reads ([lo, hi], SweepBlock) lives in a shared-memory ring of R rows x 128 paths, and while
-// block b is evaluated the CTA copies the rows that block b+1 adds with cp.async (no registers held, one barrier per block
-// — the one the regression GEMM needs anyway) and asks L2 for the rows of block b+3.  Every row comes from HBM/L2 once per
-// CTA; the evaluation reads rows with conflict-free LDS.128 at offsets the fold kernel precomputed.  The host uses this
-// variant when the windows slide upwards and fit (lsmc_api.cu), otherwise the direct-load kernel above.
+// Row-ring variant.  The profile of the kernel above shows the L1/shared-memory data pipe as the limiter: every warp reads
+// each grid point's record with broadcast loads (8 useful bytes per wavefront) and its rows of v_next through the same
+// pipe.  This variant halves the record traffic per path and removes the global loads from the evaluating threads:
+//   * a CTA is ONE group of 128 paths x 4 grid slots (4 warps); every lane owns FOUR adjacent paths, so one set of record
+//     loads serves 128 paths;
+//   * the window of v_next rows that a block of 8 grid points reads ([lo, hi], SweepBlock) lives in a shared-memory ring of
+//     R rows x 128 paths; while block b is evaluated the CTA copies the rows block b+1 adds with cp.async (no registers
+//     held; completion rides on the one barrier per block that the regression GEMM needs anyway) and asks L2 for the rows
+//     of block b+3.  Every row comes from HBM/L2 once per CTA and is read back with conflict-free LDS.128 at offsets the
+//     fold kernel precomputed.
+// The host uses it when the windows slide upwards and fit (lsmc_api.cu), otherwise the direct-load kernel above.
 // ------------------------------------------------------------------------------------------------------------------
+constexpr int kRingThreads = 128;
+constexpr int kRingWarps = kRingThreads / 32;          // = kSlots: one warp per grid slot
+constexpr int kLanePaths = 4;                          // paths per lane: two adjacent pairs ...
+constexpr int kPairGap = kSweepTilePaths / 2;          // ... this many columns apart
 constexpr int kRowBytes = kSweepTilePaths * 8;
 constexpr int kRingTabSub = 16, kRingTabRing = 2 * kRingTabSub;
+static_assert(kRingWarps == kSlots && 32 * kLanePaths == kSweepTilePaths, "one 128-path group per CTA");
+#ifndef LSMC_RING_MIN_CTAS
+#define LSMC_RING_MIN_CTAS 3
+#endif
 
+// One grid point for the lane's four paths; rows from the shared-memory ring (LSV.cs:310-336).
 template <int KP, int KC, bool FUSED>
-__device__ __forceinline__ void evaluate3_ring(const PointTable<KC> *__restrict__ t, const char *__restrict__ my_rows,
-                                               const double (&q0)[KP], const double (&q1)[KP], double price0, double price1, double df,
-                                               double &v0, double &v1) {
+__device__ __forceinline__ void evaluate4_ring(const PointTable<KC> *__restrict__ t, const char *__restrict__ my_rows,
+                                               const double (&q)[kLanePaths][KP], const double (&price)[kLanePaths], double df,
+                                               double (&v)[kLanePaths]) {
   if (FUSED) {
-    // the three decisions' dot products advance together: six independent FMA chains instead of two
-    double cont0[3], cont1[3];
-#pragma unroll
-    for (int d = 0; d < 3; ++d) {
-      cont0[d] = q0[0] * t->c[d][0];
-      cont1[d] = q1[0] * t->c[d][0];
-    }
-#pragma unroll
-    for (int k = 1; k < KP; ++k) {
-#pragma unroll
-      for (int d = 0; d < 3; ++d) {
-        cont0[d] = __fma_rn(q0[k], t->c[d][k], cont0[d]);
-        cont1[d] = __fma_rn(q1[k], t->c[d][k], cont1[d]);
-      }
-    }
-    double tt0[3], tt1[3], w0[3], w1[3];
+    double best[kLanePaths];
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
       const DecisionF f = *reinterpret_cast<const DecisionF *>(&t->a[d]);
-      const double2 lo = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d]);
-      const double2 up = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
-      const double pay0 = __fma_rn(price0, f.price_coef, f.offset), pay1 = __fma_rn(price1, f.price_coef, f.offset);
-      tt0[d] = pay0 + cont0[d];  // what the argmax is taken over (LSV.cs:317-327)
-      tt1[d] = pay1 + cont1[d];
-      w0[d] = pay0 + __fma_rn(up.x, f.upper_w, lo.x * f.lower_w);  // payoff + realised continuation (LSV.cs:296-302)
-      w1[d] = pay1 + __fma_rn(up.y, f.upper_w, lo.y * f.lower_w);
-    }
-    double best0 = tt0[0], best1 = tt1[0];
-    v0 = w0[0];
-    v1 = w1[0];
+      const double *c = t->c[d];
+      const double2 lo01 = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d]);
+      const double2 lo23 = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d] + kPairGap * 8);
+      const double2 up01 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
+      const double2 up23 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d] + kPairGap * 8);
+      const double lo[kLanePaths] = {lo01.x, lo01.y, lo23.x, lo23.y}, up[kLanePaths] = {up01.x, up01.y, up23.x, up23.y};
+      double cont[kLanePaths];
 #pragma unroll
-    for (int d = 1; d < 3; ++d) {  // first maximum wins (SH.cs:206-221)
-      if (tt0[d] > best0) {
-        best0 = tt0[d];
-        v0 = w0[d];
+      for (int j = 0; j < kLanePaths; ++j) cont[j] = q[j][0] * c[0];
+#pragma unroll
+      for (int k = 1; k < KP; ++k) {
+#pragma unroll
+        for (int j = 0; j < kLanePaths; ++j) cont[j] = __fma_rn(q[j][k], c[k], cont[j]);
       }
-      if (tt1[d] > best1) {
-        best1 = tt1[d];
-        v1 = w1[d];
+#pragma unroll
+      for (int j = 0; j < kLanePaths; ++j) {
+        const double pay = __fma_rn(price[j], f.price_coef, f.offset);
+        const double tt = pay + cont[j];                                       // what the argmax is taken over (LSV.cs:317-327)
+        const double w = pay + __fma_rn(up[j], f.upper_w, lo[j] * f.lower_w);  // payoff + realised continuation (LSV.cs:296-302)
+        if (d == 0 || tt > best[j]) {  // first maximum wins (SH.cs:206-221)
+          best[j] = tt;
+          v[j] = w;
+        }
       }
     }
   } else {
-    double best0 = 0.0, best1 = 0.0, adj0 = 0.0, adj1 = 0.0;
+    double best[kLanePaths] = {0.0, 0.0, 0.0, 0.0}, adj[kLanePaths] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-      const double2 lo = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d]);
-      const double2 up = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
-      evaluate_decision<KP>(d == 0, t->a[d], t->upper_w[d], t->c[d], lo, up, q0, q1, price0, price1, df, t->inv_cost, best0, best1, adj0,
-                            adj1);
+      const double2 lo01 = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d]);
+      const double2 lo23 = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d] + kPairGap * 8);
+      const double2 up01 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
+      const double2 up23 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d] + kPairGap * 8);
+      evaluate_decision<KP>(d == 0, t->a[d], t->upper_w[d], t->c[d], lo01, up01, q[0], q[1], price[0], price[1], df, t->inv_cost,
+                            best[0], best[1], adj[0], adj[1]);
+      evaluate_decision<KP>(d == 0, t->a[d], t->upper_w[d], t->c[d], lo23, up23, q[2], q[3], price[2], price[3], df, t->inv_cost,
+                            best[2], best[3], adj[2], adj[3]);
     }
-    v0 = best0 + adj0;  // LSV.cs:333
-    v1 = best1 + adj1;
+#pragma unroll
+    for (int j = 0; j < kLanePaths; ++j) v[j] = best[j] + adj[j];  // LSV.cs:333
   }
 }
 
 template <int KP, bool FUSED>
-__global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_sweep_ring_kernel(BackwardStepArgs a) {
+__global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_sweep_ring_kernel(BackwardStepArgs a) {
   constexpr int KC = (KP + 1) & ~1;
   constexpr int MB = KP <= 8 ? 1 : 2;
   constexpr int ACC = 8 * MB;
+  constexpr int CH = kSweepTilePaths / 4 / kRingWarps;  // k-chunks of 4 paths per warp in the regression GEMM (8)
   using Table = PointTable<KC>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Table *s_tab = reinterpret_cast<Table *>(smem_raw);                        // [kRingTabRing]
   double *s_v = reinterpret_cast<double *>(s_tab + kRingTabRing);            // [2][kBlockG][kVPitch]
-  double *s_acc = s_v + 2 * kBlockG * kVPitch;                               // [2][kSweepWarps][kBlockG][ACC]
-  char *s_rows = reinterpret_cast<char *>(s_acc + 2 * kSweepWarps * kBlockG * ACC);  // [R][kRowBytes]
+  double *s_acc = s_v + 2 * kBlockG * kVPitch;                               // [2][kRingWarps][ACC][kBlockG]
+  char *s_rows = reinterpret_cast<char *>(s_acc + 2 * kRingWarps * ACC * kBlockG);  // [R][kRowBytes]
   const int R = a.ring_rows;
   SweepBlock *s_blk = reinterpret_cast<SweepBlock *>(s_rows + (size_t)R * kRowBytes);  // [a.subtiles_per_cta]
 
   const int K = a.K;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int slot = warp & (kSlots - 1), group = warp / kSlots;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;  // warp = grid slot
   const int64_t tile = blockIdx.y;
-  const int64_t n0 = tile * kSweepTilePaths + group * kGroupPaths + 2 * lane;
-  const bool valid0 = n0 < a.N;
-  // Columns beyond the last path are padding of the row buffers: zero in the basis rows and in the terminal values, hence
-  // finite in every row; threads that own them compute on them but never store, and the q_prev fragments are zero there.
-  const int64_t c0 = valid0 ? n0 : ((a.N - 1) & ~int64_t(1));
-  const int64_t c1 = min(c0 + 1, a.N - 1);
+  // the lane's paths: the pair (2 lane, 2 lane + 1) of the tile and the pair 64 columns further, so that every 16-byte
+  // access of a warp is one contiguous 512-byte run (no shared-memory bank conflicts, fully coalesced global accesses)
+  const int64_t n0 = tile * kSweepTilePaths + 2 * lane;
+  const bool validA = n0 < a.N, validB = n0 + kPairGap < a.N;
+  // Columns in [N, pitch) are padding of the row buffers: zero in the basis rows and in the terminal values, hence finite
+  // in every row.  Lanes that own them compute on them like on any other column; a pair that straddles N is stored (and
+  // stays finite), a pair entirely beyond N is not.  Padding never reaches the regression sums: the q_prev fragments are
+  // zero beyond N.
+  const int64_t c0 = n0;
 
   const int total_blocks = (a.G + kBlockG - 1) / kBlockG;
   const int bbeg = blockIdx.x * a.subtiles_per_cta;
@@ -437,7 +446,7 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
     const char *src = reinterpret_cast<const char *>(tab + first);
     char *dst = reinterpret_cast<char *>(s_tab + (sub & 1) * kRingTabSub);
     const int chunks = count * (int)(sizeof(Table) / 16);
-    for (int i = threadIdx.x; i < chunks; i += kSweepThreads) cp_async_16(dst + 16 * i, src + 16 * i);
+    for (int i = threadIdx.x; i < chunks; i += kRingThreads) cp_async_16(dst + 16 * i, src + 16 * i);
   };
   // rows [first_row, first_row + count) of this tile's 128 columns into ring slots first_slot.. (mod R): one warp per row,
   // two 16-byte pieces per lane
@@ -445,7 +454,7 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
   const char *tile_rows = reinterpret_cast<const char *>(a.v_next + tile * kSweepTilePaths) + lane * 16;
   char *ring_dst = s_rows + lane * 16;
   auto fetch_rows = [&](int first_row, int first_slot, int count) {
-    for (int j = warp; j < count; j += kSweepWarps) {
+    for (int j = warp; j < count; j += kRingWarps) {
       int s = first_slot + j;
       if (s >= R) s -= R;
       const char *src = row_address(tile_rows, (uint32_t)(first_row + j), pitch_bytes);
@@ -456,7 +465,7 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
   };
   auto request_rows = [&](int first_row, int count) {  // into L2 only: one 128-byte line per lane, lanes 0..7
     if (lane < 8)
-      for (int j = warp; j < count; j += kSweepWarps)
+      for (int j = warp; j < count; j += kRingWarps)
         asm volatile("prefetch.global.L2 [%0];" ::"l"(row_address(tile_rows, (uint32_t)(first_row + j), pitch_bytes) + lane * 112));
   };
 
@@ -468,58 +477,65 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
     if (nblocks > 1) request_rows(w.hi + 1, blk[1].hi - w.hi);
     if (nblocks > 2) request_rows(blk[1].hi + 1, blk[2].hi - blk[1].hi);
   }
-  for (int i = threadIdx.x; i < nblocks; i += kSweepThreads) s_blk[i] = blk[i];
+  for (int i = threadIdx.x; i < nblocks; i += kRingThreads) s_blk[i] = blk[i];
 
-  double price0, price1;
-  if (a.spot) {
-    price0 = a.spot[c0];
-    price1 = a.spot[c1];
-  } else {
-    price0 = price1 = a.const_price;
-  }
-  double q0[KP], q1[KP];
+  double price[kLanePaths];
+#pragma unroll
+  for (int j = 0; j < kLanePaths; ++j)
+    price[j] = a.spot ? a.spot[min(c0 + (j & 1) + (j >> 1) * kPairGap, a.N - 1)] : a.const_price;
+  // orthonormal basis rows of this period for the lane's four paths (continuation value = q . c)
+  double q[kLanePaths][KP];
 #pragma unroll
   for (int k = 0; k < KP; ++k) {
-    q0[k] = q1[k] = 0.0;
+#pragma unroll
+    for (int j = 0; j < kLanePaths; ++j) q[j][k] = 0.0;
     if (k < K && a.q_this) {
-      const double2 t = *reinterpret_cast<const double2 *>(a.q_this + (size_t)k * a.pitch + c0);
-      q0[k] = t.x;
-      q1[k] = t.y;
+      const double2 t01 = *reinterpret_cast<const double2 *>(a.q_this + (size_t)k * a.pitch + c0);
+      const double2 t23 = *reinterpret_cast<const double2 *>(a.q_this + (size_t)k * a.pitch + c0 + kPairGap);
+      q[0][k] = t01.x;
+      q[1][k] = t01.y;
+      q[2][k] = t23.x;
+      q[3][k] = t23.y;
     }
   }
-  if (!a.q_this) q0[0] = q1[0] = 1.0;  // mean mode: continuation value = gamma[g][0]
+  if (!a.q_this) {
+#pragma unroll
+    for (int j = 0; j < kLanePaths; ++j) q[j][0] = 1.0;  // mean mode: continuation value = gamma[g][0]
+  }
 
+  // A operand of the regression GEMM for this warp's 32-path slice of the CTA: q_prev[k][slice], fragment layout of
+  // mma.m8n8k4 (row = lane / 4 -> k, col = lane % 4 -> path inside a chunk of 4).  Paths beyond N contribute zero.
   const int row = lane >> 2, col = lane & 3;
-  double afrag[MB][4];
+  double afrag[MB][CH];
 #pragma unroll
   for (int mb = 0; mb < MB; ++mb) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < CH; ++j) {
       const int k = mb * 8 + row;
-      const int64_t p = tile * kSweepTilePaths + 16 * warp + 4 * j + col;
-      double v = 0.0;
-      if (a.accumulate && k < K && p < a.N) v = a.q_prev ? a.q_prev[(size_t)k * a.pitch + p] : (k == 0 ? 1.0 : 0.0);
-      afrag[mb][j] = v;
+      const int64_t p = tile * kSweepTilePaths + 4 * CH * warp + 4 * j + col;
+      double x = 0.0;
+      if (a.accumulate && k < K && p < a.N) x = a.q_prev ? a.q_prev[(size_t)k * a.pitch + p] : (k == 0 ? 1.0 : 0.0);
+      afrag[mb][j] = x;
     }
   }
 
   const double df = a.settle_df;
   const int last = glimit - 1;
-  char *vout = reinterpret_cast<char *>(a.v_this + (size_t)gbeg * a.pitch + n0) + (uint64_t)slot * pitch_bytes;
-  const char *my_rows = s_rows + group * (kGroupPaths * 8) + lane * 16;            // this thread's two columns of every ring row
-  double *my_v = s_v + (size_t)slot * kVPitch + group * kGroupPaths + 2 * lane;
-  const double *my_b = s_v + (size_t)row * kVPitch + 16 * warp + col;
-  double *my_c = s_acc + (size_t)warp * kBlockG * ACC + (2 * col) * ACC + row;
+  char *vout = reinterpret_cast<char *>(a.v_this + (size_t)gbeg * a.pitch + n0) + (uint64_t)warp * pitch_bytes;
+  const char *my_rows = s_rows + lane * 16;                     // this lane's first pair of columns in every ring row
+  double *my_v = s_v + (size_t)warp * kVPitch + 2 * lane;       // + buffer; second point kSlots rows further
+  const double *my_b = s_v + (size_t)row * kVPitch + 4 * CH * warp + col;      // B fragments of this warp's slice
+  double *my_c = s_acc + (size_t)warp * ACC * kBlockG + row * kBlockG + 2 * col;  // C fragment: [k][g], two adjacent g per lane
 
-  auto combine = [&](int b) {
+  auto combine = [&](int b) {  // partial sums of block b: the warps' slices added in warp order
     if (threadIdx.x < kBlockG * ACC) {
-      const int g8 = threadIdx.x / ACC, k = threadIdx.x - g8 * ACC;
+      const int k = threadIdx.x / kBlockG, g8 = threadIdx.x - k * kBlockG;
       const int g = b * kBlockG + g8;
       if (g < glimit) {
-        const double *src = s_acc + (size_t)(b & 1) * kSweepWarps * kBlockG * ACC + g8 * ACC + k;
+        const double *src = s_acc + (size_t)(b & 1) * kRingWarps * ACC * kBlockG + threadIdx.x;
         double sum = src[0];
 #pragma unroll
-        for (int w = 1; w < kSweepWarps; ++w) sum += src[(size_t)w * kBlockG * ACC];
+        for (int w = 1; w < kRingWarps; ++w) sum += src[(size_t)w * ACC * kBlockG];
         a.partials[((size_t)tile * a.G + gbeg + g) * ACC + k] = sum;
       }
     }
@@ -536,37 +552,44 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
       fetch_rows(cur.hi + 1, cur.hi_slot + 1, nxt.hi - cur.hi);
       if (b + 3 < nblocks) request_rows(s_blk[b + 2].hi + 1, s_blk[b + 3].hi - s_blk[b + 2].hi);
     }
-    const int gA = b * kBlockG + slot, gB = gA + kSlots;
+    const int gA = b * kBlockG + warp, gB = gA + kSlots;
     const Table *tA = s_tab + (min(gA, last) & (kRingTabRing - 1));
     const Table *tB = s_tab + (min(gB, last) & (kRingTabRing - 1));
-    double vA0, vA1, vB0, vB1;
-    evaluate3_ring<KP, KC, FUSED>(tA, my_rows, q0, q1, price0, price1, df, vA0, vA1);
-    evaluate3_ring<KP, KC, FUSED>(tB, my_rows, q0, q1, price0, price1, df, vB0, vB1);
-    if (valid0) {
-      if (gA <= last) *reinterpret_cast<double2 *>(vout) = make_double2(vA0, vA1);
-      if (gB <= last) *reinterpret_cast<double2 *>(vout + (uint64_t)kSlots * pitch_bytes) = make_double2(vB0, vB1);
+    double vA[kLanePaths], vB[kLanePaths];
+    evaluate4_ring<KP, KC, FUSED>(tA, my_rows, q, price, df, vA);
+    evaluate4_ring<KP, KC, FUSED>(tB, my_rows, q, price, df, vB);
+    if (gA <= last) {
+      if (validA) *reinterpret_cast<double2 *>(vout) = make_double2(vA[0], vA[1]);
+      if (validB) *reinterpret_cast<double2 *>(vout + kPairGap * 8) = make_double2(vA[2], vA[3]);
+    }
+    if (gB <= last) {
+      char *vo = vout + (uint64_t)kSlots * pitch_bytes;
+      if (validA) *reinterpret_cast<double2 *>(vo) = make_double2(vB[0], vB[1]);
+      if (validB) *reinterpret_cast<double2 *>(vo + kPairGap * 8) = make_double2(vB[2], vB[3]);
     }
     vout += (uint64_t)kBlockG * pitch_bytes;
     const int buf = b & 1;
     if (a.accumulate) {
       double *vt = my_v + buf * (kBlockG * kVPitch);
-      *reinterpret_cast<double2 *>(vt) = make_double2(vA0, vA1);
-      *reinterpret_cast<double2 *>(vt + kSlots * kVPitch) = make_double2(vB0, vB1);
+      *reinterpret_cast<double2 *>(vt) = make_double2(vA[0], vA[1]);
+      *reinterpret_cast<double2 *>(vt + kPairGap) = make_double2(vA[2], vA[3]);
+      *reinterpret_cast<double2 *>(vt + kSlots * kVPitch) = make_double2(vB[0], vB[1]);
+      *reinterpret_cast<double2 *>(vt + kSlots * kVPitch + kPairGap) = make_double2(vB[2], vB[3]);
     }
     cp_async_wait_all();  // this thread's share of the next block's rows (and table records) has landed ...
     __syncthreads();      // ... and so has everybody else's
     if (a.accumulate) {
+      // C[k][g] = sum over the warp's 32 paths of q_prev[k][n] * V[g][n]; C fragment: row -> k, columns 2 col + {0,1} -> g
       const double *vb = my_b + buf * (kBlockG * kVPitch);
-      double *dst = my_c + buf * (kSweepWarps * kBlockG * ACC);
+      double *dst = my_c + buf * (kRingWarps * ACC * kBlockG);
 #pragma unroll
       for (int mb = 0; mb < MB; ++mb) {
         double acc0 = 0.0, acc1 = 0.0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dmma_m8n8k4(acc0, acc1, afrag[mb][j], vb[4 * j]);
-        dst[mb * 8] = acc0;
-        dst[ACC + mb * 8] = acc1;
+        for (int j = 0; j < CH; ++j) dmma_m8n8k4(acc0, acc1, afrag[mb][j], vb[4 * j]);
+        *reinterpret_cast<double2 *>(dst + mb * 8 * kBlockG) = make_double2(acc0, acc1);
       }
-      if (b > 0) combine(b - 1);
+      if (b > 0) combine(b - 1);  // complete since the barrier above
     }
   }
   if (a.accumulate) {
@@ -579,10 +602,10 @@ template <int KP>
 void launch_sweep_ring_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
   if (a.fused_payoff) {
     cudaFuncSetAttribute(backward_sweep_ring_kernel<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    backward_sweep_ring_kernel<KP, true><<<grid, kSweepThreads, smem, stream>>>(a);
+    backward_sweep_ring_kernel<KP, true><<<grid, kRingThreads, smem, stream>>>(a);
   } else {
     cudaFuncSetAttribute(backward_sweep_ring_kernel<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    backward_sweep_ring_kernel<KP, false><<<grid, kSweepThreads, smem, stream>>>(a);
+    backward_sweep_ring_kernel<KP, false><<<grid, kRingThreads, smem, stream>>>(a);
   }
 }
 
@@ -626,7 +649,7 @@ size_t backward_sweep_smem_bytes(int K) {
 size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta) {
   const int KP = padded_basis(K);
   const int ACC = KP <= 8 ? 8 : 16;
-  return point_table_bytes(K) * kRingTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kSweepWarps * kBlockG * ACC) +
+  return point_table_bytes(K) * kRingTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kRingWarps * kBlockG * ACC) +
          (size_t)ring_rows * kRowBytes + (size_t)blocks_per_cta * sizeof(SweepBlock);
 }
 
