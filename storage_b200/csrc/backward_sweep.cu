@@ -446,6 +446,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
     const char *src = reinterpret_cast<const char *>(tab + first);
     char *dst = reinterpret_cast<char *>(s_tab + (sub & 1) * kRingTabSub);
     const int chunks = count * (int)(sizeof(Table) / 16);
+#pragma unroll 1
     for (int i = threadIdx.x; i < chunks; i += kRingThreads) cp_async_16(dst + 16 * i, src + 16 * i);
   };
   // rows [first_row, first_row + count) of this tile's 128 columns into ring slots first_slot.. (mod R): one warp per row,
@@ -454,6 +455,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   const char *tile_rows = reinterpret_cast<const char *>(a.v_next + tile * kSweepTilePaths) + lane * 16;
   char *ring_dst = s_rows + lane * 16;
   auto fetch_rows = [&](int first_row, int first_slot, int count) {
+#pragma unroll 1
     for (int j = warp; j < count; j += kRingWarps) {
       int s = first_slot + j;
       if (s >= R) s -= R;
@@ -465,6 +467,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   };
   auto request_rows = [&](int first_row, int count) {  // into L2 only: one 128-byte line per lane, lanes 0..7
     if (lane < 8)
+#pragma unroll 1
       for (int j = warp; j < count; j += kRingWarps)
         asm volatile("prefetch.global.L2 [%0];" ::"l"(row_address(tile_rows, (uint32_t)(first_row + j), pitch_bytes) + lane * 112));
   };
