@@ -363,9 +363,17 @@ __device__ __forceinline__ void evaluate4_ring(const PointTable<KC> *__restrict_
       const double *c = t->c[d];
       const double2 lo01 = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d]);
       const double2 lo23 = *reinterpret_cast<const double2 *>(my_rows + t->lower_row[d] + kPairGap * 8);
-      const double2 up01 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
-      const double2 up23 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d] + kPairGap * 8);
-      const double lo[kLanePaths] = {lo01.x, lo01.y, lo23.x, lo23.y}, up[kLanePaths] = {up01.x, up01.y, up23.x, up23.y};
+      // realised continuation value (LSV.cs:296-302).  A decision that lands exactly on a grid point of the next period has
+      // lower == upper and weights (1, 0): the interpolation returns the row itself, bit for bit, so it is not re-read.
+      double real[kLanePaths] = {lo01.x, lo01.y, lo23.x, lo23.y};
+      if (t->lower_row[d] != t->upper_row[d]) {  // warp-uniform
+        const double2 up01 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d]);
+        const double2 up23 = *reinterpret_cast<const double2 *>(my_rows + t->upper_row[d] + kPairGap * 8);
+        real[0] = __fma_rn(up01.x, f.upper_w, real[0] * f.lower_w);
+        real[1] = __fma_rn(up01.y, f.upper_w, real[1] * f.lower_w);
+        real[2] = __fma_rn(up23.x, f.upper_w, real[2] * f.lower_w);
+        real[3] = __fma_rn(up23.y, f.upper_w, real[3] * f.lower_w);
+      }
       double cont[kLanePaths];
 #pragma unroll
       for (int j = 0; j < kLanePaths; ++j) cont[j] = q[j][0] * c[0];
@@ -378,7 +386,7 @@ __device__ __forceinline__ void evaluate4_ring(const PointTable<KC> *__restrict_
       for (int j = 0; j < kLanePaths; ++j) {
         const double pay = __fma_rn(price[j], f.price_coef, f.offset);
         const double tt = pay + cont[j];                                       // what the argmax is taken over (LSV.cs:317-327)
-        const double w = pay + __fma_rn(up[j], f.upper_w, lo[j] * f.lower_w);  // payoff + realised continuation (LSV.cs:296-302)
+        const double w = pay + real[j];
         if (d == 0 || tt > best[j]) {  // first maximum wins (SH.cs:206-221)
           best[j] = tt;
           v[j] = w;
