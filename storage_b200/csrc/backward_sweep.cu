@@ -375,12 +375,14 @@ __device__ __forceinline__ void evaluate4_ring(const PointTable<KC> *__restrict_
         real[3] = __fma_rn(up23.y, f.upper_w, real[3] * f.lower_w);
       }
       double cont[kLanePaths];
+      {
 #pragma unroll
-      for (int j = 0; j < kLanePaths; ++j) cont[j] = q[j][0] * c[0];
+        for (int j = 0; j < kLanePaths; ++j) cont[j] = q[j][0] * c[0];
 #pragma unroll
-      for (int k = 1; k < KP; ++k) {
+        for (int k = 1; k < KP; ++k) {
 #pragma unroll
-        for (int j = 0; j < kLanePaths; ++j) cont[j] = __fma_rn(q[j][k], c[k], cont[j]);
+          for (int j = 0; j < kLanePaths; ++j) cont[j] = __fma_rn(q[j][k], c[k], cont[j]);
+        }
       }
 #pragma unroll
       for (int j = 0; j < kLanePaths; ++j) {
