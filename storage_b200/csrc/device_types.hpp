@@ -102,6 +102,7 @@ struct ForwardArgs {
   double *final_inventory;         // [N]
   double *step_sums;               // [P][num_ctas][kForwardSums + K]
   int sums_width;
+  int tiles_per_cta;               // 128-path tiles each CTA carries through all periods (state kept in shared memory)
   // optional panels [P+1][N] (NULL = not requested)
   double *p_inventory, *p_volume, *p_consumed, *p_loss, *p_net_volume, *p_pv, *p_decision;
   int32_t *error_flag;             // set to an lsmc_status when a path leaves the feasible region

@@ -651,34 +651,49 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
   double *s_grid = s_gamma + (size_t)a.Gmax * K;
   dd *s_rinv = reinterpret_cast<dd *>(s_grid + a.Gmax);
   double *s_stage = reinterpret_cast<double *>(s_rinv + K * K);  // [kWarps][sums_width]
-  int32_t *s_pw = reinterpret_cast<int32_t *>(s_stage + kWarps * a.sums_width);
+  double *s_inv = s_stage + kWarps * a.sums_width;                // [tiles_per_cta][kThreads] inventory carried by each path
+  double *s_pv = s_inv + (size_t)a.tiles_per_cta * kThreads;       // [tiles_per_cta][kThreads] PV accumulated so far
+  int32_t *s_pw = reinterpret_cast<int32_t *>(s_pv + (size_t)a.tiles_per_cta * kThreads);
   __shared__ DevPeriodParams s_pp;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
 
+  // A CTA owns tiles blockIdx.x, blockIdx.x + gridDim.x, ... (at most a.tiles_per_cta of them).  Periods are the outer loop so
+  // that the period's tables (regression coefficients, next grid, R^-1) are staged once per CTA and period; the state a path
+  // carries from one period to the next (inventory, PV so far) waits in shared memory.
   const int64_t num_tiles = (a.N + kThreads - 1) / kThreads;
-  bool first_tile = true;
-  for (int64_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, first_tile = false) {
-    const int64_t n = tile * kThreads + threadIdx.x;
-    const bool valid = n < a.N;
-    const int64_t nc = valid ? n : a.N - 1;
-    double inventory = a.start_inventory;
-    double pv_total = 0.0;
-    int err = 0;
+  for (int t = 0; t < a.tiles_per_cta; ++t) {
+    s_inv[t * kThreads + threadIdx.x] = a.start_inventory;
+    s_pv[t * kThreads + threadIdx.x] = 0.0;
+  }
+  int err = 0;
 
-    for (int p = 0; p < a.P; ++p) {
-      __syncthreads();  // previous period's shared tables are no longer in use
-      if (threadIdx.x == 0) s_pp = a.periods[p];
-      __syncthreads();
-      const DevPeriodParams pp = s_pp;
-      const int Gn = pp.grid_next_count;
-      for (int i = threadIdx.x; i < Gn * K; i += blockDim.x) s_gamma[i] = a.gamma[(size_t)p * a.Gmax * K + i];
-      for (int i = threadIdx.x; i < Gn; i += blockDim.x) s_grid[i] = a.grids[(size_t)(p + 1) * a.Gmax + i];
-      if (!pp.mean_mode)
-        for (int i = threadIdx.x; i < K * K; i += blockDim.x)
-          s_rinv[i] = dd{a.rinv[((size_t)p * K * K + i) * 2], a.rinv[((size_t)p * K * K + i) * 2 + 1]};
-      __syncthreads();
+  for (int p = 0; p < a.P; ++p) {
+    __syncthreads();  // previous period's shared tables are no longer in use
+    if (threadIdx.x == 0) s_pp = a.periods[p];
+    __syncthreads();
+    const DevPeriodParams pp = s_pp;
+    const int Gn = pp.grid_next_count;
+    for (int i = threadIdx.x; i < Gn * K; i += blockDim.x) s_gamma[i] = a.gamma[(size_t)p * a.Gmax * K + i];
+    for (int i = threadIdx.x; i < Gn; i += blockDim.x) s_grid[i] = a.grids[(size_t)(p + 1) * a.Gmax + i];
+    if (!pp.mean_mode)
+      for (int i = threadIdx.x; i < K * K; i += blockDim.x)
+        s_rinv[i] = dd{a.rinv[((size_t)p * K * K + i) * 2], a.rinv[((size_t)p * K * K + i) * 2 + 1]};
+    __syncthreads();
+
+    double sums[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // this thread's paths, tile after tile
+    double qsum[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) qsum[k] = 0.0;
+
+    for (int t = 0; t < a.tiles_per_cta; ++t) {
+      const int64_t tile = blockIdx.x + (int64_t)t * gridDim.x;
+      if (tile >= num_tiles) break;
+      const int64_t n = tile * kThreads + threadIdx.x;
+      const bool valid = n < a.N;
+      const int64_t nc = valid ? n : a.N - 1;
+      double inventory = s_inv[t * kThreads + threadIdx.x];
 
       BasisSpec b;
       b.mean_mode = pp.mean_mode;
@@ -754,43 +769,50 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
         if (a.p_decision) a.p_decision[off] = (double)best_d;
       }
 
-      // per-period sums (LSV.cs:490-507, 510): fixed-order reduction over the CTA
-      double sums[8];
-      sums[0] = valid ? -(best_volume + best_consumed) * price : 0.0;
-      sums[1] = valid ? best_volume : 0.0;
-      sums[2] = valid ? best_consumed : 0.0;
-      sums[3] = valid ? loss : 0.0;
-      sums[4] = valid ? best_immediate : 0.0;
-      sums[5] = valid ? inventory : 0.0;
-      sums[6] = 0.0;
-      sums[7] = 0.0;
-      int kidx;
-      double total = warp_reduce8(sums, lane, kidx);
-      if ((lane & 3) == 0) s_stage[warp * a.sums_width + kidx] = total;
-      for (int half = 0; half < KP; half += 8) {
-        double part[8];
+      // per-period sums (LSV.cs:490-507, 510)
+      if (valid) {
+        sums[0] += -(best_volume + best_consumed) * price;
+        sums[1] += best_volume;
+        sums[2] += best_consumed;
+        sums[3] += loss;
+        sums[4] += best_immediate;
+        sums[5] += inventory;
+        s_pv[t * kThreads + threadIdx.x] += best_immediate;
+      }
 #pragma unroll
-        for (int k = 0; k < 8; ++k) part[k] = (half + k < KP) ? q[(half + k < KP) ? half + k : 0] : 0.0;
-        total = warp_reduce8(part, lane, kidx);
-        if ((lane & 3) == 0 && half + kidx < K) s_stage[warp * a.sums_width + kForwardSums + half + kidx] = total;
-      }
-      __syncthreads();
-      if (threadIdx.x < a.sums_width) {
-        double t = s_stage[threadIdx.x];
-        for (int w = 1; w < kWarps; ++w) t += s_stage[w * a.sums_width + threadIdx.x];
-        double *dst = a.step_sums + ((size_t)p * gridDim.x + blockIdx.x) * a.sums_width + threadIdx.x;
-        *dst = first_tile ? t : *dst + t;
-      }
-      if (valid) pv_total += best_immediate;
-      inventory = next_inventory;
+      for (int k = 0; k < KP; ++k) qsum[k] += q[k];
+      s_inv[t * kThreads + threadIdx.x] = next_inventory;
     }
-    if (valid) {
-      a.pv_by_sim[n] = pv_total;
+
+    // fixed-order reduction over the CTA
+    int kidx;
+    double total = warp_reduce8(sums, lane, kidx);
+    if ((lane & 3) == 0) s_stage[warp * a.sums_width + kidx] = total;
+    for (int half = 0; half < KP; half += 8) {
+      double part[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) part[k] = (half + k < KP) ? qsum[(half + k < KP) ? half + k : 0] : 0.0;
+      total = warp_reduce8(part, lane, kidx);
+      if ((lane & 3) == 0 && half + kidx < K) s_stage[warp * a.sums_width + kForwardSums + half + kidx] = total;
+    }
+    __syncthreads();
+    if (threadIdx.x < a.sums_width) {
+      double t = s_stage[threadIdx.x];
+      for (int w = 1; w < kWarps; ++w) t += s_stage[w * a.sums_width + threadIdx.x];
+      a.step_sums[((size_t)p * gridDim.x + blockIdx.x) * a.sums_width + threadIdx.x] = t;
+    }
+  }
+  for (int t = 0; t < a.tiles_per_cta; ++t) {
+    const int64_t tile = blockIdx.x + (int64_t)t * gridDim.x;
+    const int64_t n = tile * kThreads + threadIdx.x;
+    if (tile < num_tiles && n < a.N) {
+      const double inventory = s_inv[t * kThreads + threadIdx.x];
+      a.pv_by_sim[n] = s_pv[t * kThreads + threadIdx.x];
       a.final_inventory[n] = inventory;
       if (a.p_inventory) a.p_inventory[(size_t)a.P * a.N + n] = inventory;
     }
-    if (err) atomicExch(a.error_flag, err);
   }
+  if (err) atomicExch(a.error_flag, err);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -901,9 +923,9 @@ size_t backward_smem_bytes(int KP, int D) {
                                                 (size_t)kWarps * acc * tg + tg) + sizeof(int32_t) * tg + 16;
 }
 
-size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width) {
+size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width, int tiles_per_cta) {
   return sizeof(double) * ((size_t)Gmax * K + Gmax) + sizeof(dd) * K * K + sizeof(double) * kWarps * sums_width +
-         sizeof(int32_t) * K * (1 + F) + 16;
+         sizeof(double) * 2 * (size_t)tiles_per_cta * kThreads + sizeof(int32_t) * K * (1 + F) + 16;
 }
 
 void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream) {
@@ -924,7 +946,7 @@ void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream) {
   reduce_partials_kernel<<<a.G, threads, 0, stream>>>(a);
 }
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream) {
-  dispatch(padded_basis(a.K), 3, &a, dim3(num_ctas), dim3(kThreads), forward_smem_bytes(a.K, a.F, a.Gmax, a.sums_width), stream);
+  dispatch(padded_basis(a.K), 3, &a, dim3(num_ctas), dim3(kThreads), forward_smem_bytes(a.K, a.F, a.Gmax, a.sums_width, a.tiles_per_cta), stream);
 }
 void launch_combine_ranks(const double *all, int world, int count, int K, int mean_mode, double total_paths, double *out,
                           cudaStream_t stream) {

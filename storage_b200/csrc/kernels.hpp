@@ -60,7 +60,7 @@ struct FoldArgs {
 int padded_basis(int K);
 inline int acc_width(int K) { return padded_basis(K) <= 8 ? 8 : 16; }
 size_t backward_smem_bytes(int KP, int D);
-size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width);
+size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width, int tiles_per_cta);
 
 void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream);
 void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream);

@@ -659,7 +659,9 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   // ---- forward simulation (LSV.cs:390-521)
   t_fwd.start();
   const int sums_width = kForwardSums + K;
-  const int fwd_ctas = (int)std::min<int64_t>((N + kThreads - 1) / kThreads, (int64_t)sm_count * 8);
+  const int64_t fwd_tiles = (N + kThreads - 1) / kThreads;
+  constexpr int kForwardMaxTiles = 8;  // per-path state of this many tiles fits beside the period tables in shared memory
+  const int fwd_ctas = (int)std::max<int64_t>(std::min<int64_t>(fwd_tiles, (int64_t)sm_count * 8), (fwd_tiles + kForwardMaxTiles - 1) / kForwardMaxTiles);
   if (h->step_sums.count < (size_t)P * fwd_ctas * sums_width) h->step_sums.allocate((size_t)P * fwd_ctas * sums_width);
   if (h->step_totals.count < (size_t)P * sums_width) h->step_totals.allocate((size_t)P * sums_width);
   ForwardArgs fa{};
@@ -688,6 +690,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.final_inventory = h->final_inv.ptr;
   fa.step_sums = h->step_sums.ptr;
   fa.sums_width = sums_width;
+  fa.tiles_per_cta = (int)((fwd_tiles + fwd_ctas - 1) / fwd_ctas);
   fa.p_inventory = h->panels[0].ptr;
   fa.p_volume = h->panels[1].ptr;
   fa.p_consumed = h->panels[2].ptr;
