@@ -93,9 +93,11 @@ struct lsmc_handle {
   int Gmax = 0, D = 0, acc_k = 8;
 
   cudaStream_t stream = nullptr;
+  cudaStream_t aux_stream = nullptr;          // basis rows of period p-3 are materialised here while step p-1 runs
+  cudaEvent_t ev_basis[3] = {}, ev_step[3] = {}, ev_prepass = nullptr;
   SimSet sims[2];
   DeviceBuffer<double> v_a, v_b, grids, gamma, rinv, partials, gram_partials, inv_cost, pv, final_inv, step_sums, step_totals,
-      block_sums, gather_buf, qbuf[2], ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
+      block_sums, gather_buf, qbuf[3], ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
   DeviceBuffer<DevDecision> decisions;
   DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag, win_lo, win_hi;
@@ -436,6 +438,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   auto check_cancel = [&] {
     if (cancelled()) {
       cudaStreamSynchronize(st);
+      cudaStreamSynchronize(h->aux_stream);
       throw Error(LSMC_ERR_CANCELLED, "The operation was canceled.");
     }
   };
@@ -509,7 +512,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   int sm_count = 148;
   cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device);
   static const bool use_sweep = [] { const char *e = std::getenv("LSMC_SWEEP"); return !(e && e[0] == '0'); }();  // test hook
-  auto q_buffer = [&](int period) { return h->qbuf[period & 1].ptr; };
+  auto q_buffer = [&](int period) { return h->qbuf[period % 3].ptr; };
   auto has_basis = [&](int period) { return period >= first_reg && period < P; };
   auto launch_basis_for = [&](int period) {
     // orthonormal basis rows of the regression simulations of `period` (LSV.cs:191 PopulateDesignMatrix + :193-196 QR)
@@ -521,13 +524,25 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     b.spec = basis_spec(*h, 0, period);
     b.powers = h->d_powers.ptr;
     b.q_out = q_buffer(period);
-    launch_basis(b, st);
+    launch_basis(b, h->aux_stream);
+    cudaEventRecord(h->ev_basis[period % 3], h->aux_stream);
     launches++;
-    dbg("basis_kernel", period);
+    if (debug_sync) {
+      cudaError_t e = cudaStreamSynchronize(h->aux_stream);
+      if (e == cudaSuccess) e = cudaGetLastError();
+      if (e != cudaSuccess) throw CudaFailure(std::string("basis_kernel (period ") + std::to_string(period) + ") failed: " + cudaGetErrorString(e));
+    }
   };
+  // The basis rows are independent of the value recursion, so they are produced on a second stream, three buffers deep:
+  // step p reads q(p) and q(p-1); once it has finished, the buffer of q(p) is free for q(p-3), which is then computed while
+  // step p-1 runs and is first needed by step p-2.
+  cudaEventRecord(h->ev_prepass, st);
+  cudaStreamWaitEvent(h->aux_stream, h->ev_prepass, 0);
+  if (has_basis(P - 1)) launch_basis_for(P - 1);
+  if (has_basis(P - 2)) launch_basis_for(P - 2);
   auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this) {
     const PeriodTables &pt = h->tables.periods[p];
-    if (has_basis(p - 1)) launch_basis_for(p - 1);
+    if (has_basis(p - 1)) cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0);
     BackwardStepArgs a{};
     a.N = N;
     a.pitch = h->pitch;
@@ -607,6 +622,11 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     if (!terminal) cudaEventRecord(step_events[2 * p + 1], st);
     launches++;
     dbg(ring ? "backward_ring_kernel" : sweep ? "backward_sweep_kernel" : "backward_step_kernel", p);
+    if (has_basis(p - 3)) {
+      cudaEventRecord(h->ev_step[p % 3], st);
+      cudaStreamWaitEvent(h->aux_stream, h->ev_step[p % 3], 0);
+      launch_basis_for(p - 3);
+    }
     return (int)tiles;
   };
   auto reduce_gamma = [&](int p, int G_next, int num_chunks) {
@@ -850,6 +870,10 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
 
     require_device(device);
     CUDA_OK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CUDA_OK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
+    for (auto &e : h->ev_basis) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &e : h->ev_step) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&h->ev_prepass, cudaEventDisableTiming));
     h->v_a.allocate((size_t)h->Gmax * h->pitch);
     h->v_b.allocate((size_t)h->Gmax * h->pitch);
     // the padding columns [N, pitch) of the value rows are read (never written) by the sweep kernels: keep them finite
@@ -863,6 +887,7 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     h->point_tables.allocate((size_t)h->Gmax * point_table_bytes(h->K) / sizeof(double));
     h->qbuf[0].allocate((size_t)h->K * h->pitch);
     h->qbuf[1].allocate((size_t)h->K * h->pitch);
+    h->qbuf[2].allocate((size_t)h->K * h->pitch);
     h->pv.allocate(h->N);
     h->final_inv.allocate(h->N);
     h->error_flag.allocate(1);
@@ -1071,7 +1096,12 @@ void lsmc_destroy(lsmc_handle *h) {
   cudaSetDevice(h->device);
   if (h->stream) {
     cudaStreamSynchronize(h->stream);
+    if (h->aux_stream) cudaStreamSynchronize(h->aux_stream);
     cudaStreamDestroy(h->stream);
+    if (h->aux_stream) cudaStreamDestroy(h->aux_stream);
+    for (auto &e : h->ev_basis) if (e) cudaEventDestroy(e);
+    for (auto &e : h->ev_step) if (e) cudaEventDestroy(e);
+    if (h->ev_prepass) cudaEventDestroy(h->ev_prepass);
   }
   delete h;
 }
