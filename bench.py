@@ -312,7 +312,7 @@ def run_gpu(args):
     P = flat.num_periods
     mean_grid = evals_local / n / P
     bytes_per_launch = n * (16.0 * mean_grid + 2 * 8.0 * (1 + 3))
-    avg_kernel_s = kernel_ms / 1000.0 / max(1, bk_launches)
+    avg_kernel_s = max(kernel_ms, 1e-9) / 1000.0 / max(1, bk_launches)
     achieved = bytes_per_launch / avg_kernel_s / 1e9
     value = evals_total / step_s
     out = {"metric": "LSMC path*step*inventory-point evals/sec", "value": value, "unit": "path*step*inventory-point evals/s",

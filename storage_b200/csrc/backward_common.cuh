@@ -1,5 +1,6 @@
-// backward_common.cuh — pieces shared by the two variants of the backward-induction kernel (kernels.cu: rows of
-// v_next read through L1/L2; backward_ring.cu: rows staged once in a shared-memory ring by bulk TMA copies).
+// backward_common.cuh — pieces shared by the backward-induction kernels (kernels.cu: general kernel; backward_sweep.cu:
+// three-decision sweep kernels).
+
 #pragma once
 #include <cstdint>
 

@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
         double sum = src[0];
 #pragma unroll
         for (int w = 1; w < kSweepWarps; ++w) sum += src[(size_t)w * kBlockG * ACC];
-        a.partials[((size_t)tile * a.G + gbeg + g) * ACC + k] = sum;
+        a.partials[((size_t)(gbeg + g) * gridDim.y + tile) * ACC + k] = sum;
       }
     }
   };
@@ -549,7 +549,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
         double sum = src[0];
 #pragma unroll
         for (int w = 1; w < kRingWarps; ++w) sum += src[(size_t)w * ACC * kBlockG];
-        a.partials[((size_t)tile * a.G + gbeg + g) * ACC + k] = sum;
+        a.partials[((size_t)(gbeg + g) * gridDim.y + tile) * ACC + k] = sum;
       }
     }
   };

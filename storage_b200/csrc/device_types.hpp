@@ -53,13 +53,11 @@ struct BackwardStepArgs {
   const double *q_this; // [K][pitch] orthonormal basis rows of this period (NULL: mean mode, q = e_0)
   const double *q_prev; // [K][pitch] basis rows of period-1 for the regression sums (NULL with accumulate: mean mode)
   int accumulate;       // 0: no further regression (period 0)
-  double *partials;     // [num_tiles][G][acc] per-tile sums of q_prev[k] * v_this[g]
+  double *partials;     // [G][num_tiles][acc] per-tile sums of q_prev[k] * v_this[g] (num_tiles = gridDim.y)
   int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring and sweep kernels)
   const SweepBlock *sweep_blocks;  // row-ring sweep kernel: [blocks of 8 grid points] of this period
   const void *point_tables;  // sweep kernel: [G] per-grid-point records written by fold_tables_kernel
-  // ring kernel only: rows of v_next needed by each group of 8 grid points, and the ring size in rows
-  const int32_t *win_lo, *win_hi;
-  int ring_rows;
+  int ring_rows;        // row-ring sweep kernel: rows in the shared-memory ring (0: direct-load kernels)
   // terminal mode: v_this[g][n] = TerminalStorageNpv(spot[n], grid_this[g]) instead of the decision step
   int terminal_mode;
   int fused_payoff;     // 1: fused-payoff arithmetic (backward_common.cuh point_fused); 0: the reference's operation order

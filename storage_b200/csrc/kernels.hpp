@@ -35,7 +35,7 @@ struct BasisArgs {
 };
 
 struct ReduceArgs {
-  const double *partials;  // [num_chunks][G][acc_k]
+  const double *partials;  // [G][num_chunks][acc_k]: per path tile sums, written by the backward kernels
   int num_chunks, G, K, acc_k;
   int mean_mode;
   int64_t total_paths;
@@ -66,9 +66,6 @@ void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t 
 void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream);
 void launch_backward_step(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 void launch_basis(const BasisArgs &a, cudaStream_t stream);
-// TMA-staged variant (backward_ring.cu); gsplit CTAs per path tile, each sweeping a.subtiles_per_cta groups of 8 grid points
-size_t backward_ring_smem_bytes(int KP, int D, int ring_rows);
-void launch_backward_ring(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 // Three-decision sweep kernel (backward_sweep.cu): gsplit CTAs per 128-path tile, each sweeping a.subtiles_per_cta blocks of 8
 // grid points; partial sums are laid out [tile of 128 paths][G][acc].
 size_t point_table_bytes(int K);

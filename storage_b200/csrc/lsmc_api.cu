@@ -8,6 +8,7 @@
 #include <cmath>
 #include <climits>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -100,9 +101,8 @@ struct lsmc_handle {
       block_sums, gather_buf, qbuf[3], ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
   DeviceBuffer<DevDecision> decisions;
   DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
-  DeviceBuffer<int32_t> num_decisions, d_powers, error_flag, win_lo, win_hi;
-  std::vector<size_t> window_offset;  // per period: first group in win_lo / win_hi
-  std::vector<int> ring_rows;         // per period: ring size the TMA-staged kernel needs (0: use the direct-load kernel)
+  DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
+  std::vector<size_t> window_offset;  // per period: first block in sweep_blocks
   std::vector<int> sweep_ring_rows;   // per period: ring size of the row-ring sweep kernel (0: direct-load sweep kernel)
   DeviceBuffer<SweepBlock> sweep_blocks;  // [window_offset[p] + block] row windows of the row-ring sweep kernel
   DeviceBuffer<DevPeriodParams> period_params;
@@ -301,23 +301,16 @@ void build_device_tables(lsmc_handle *h) {
   h->num_decisions.upload(nd);
   h->inv_cost.upload(invc);
 
-  // Row windows of the next period's value slab that each group of 8 grid points reads (backward_ring.cu).  The ring
-  // variant needs the windows to slide upwards and to fit in shared memory; otherwise the period uses direct loads.
+  // Row windows of the next period's value slab that each block of 8 grid points reads, for the row-ring sweep kernel.
   {
-    constexpr int kGroup = 8, kMaxRing = 40;
-    // The TMA-staged variant is correct but currently slower than the direct-load kernel on B200 (8 warps/SM, see
-    // profiles/r01_backward_ring.txt); it is opt-in until it wins.
-    const char *ring_env = std::getenv("LSMC_RING");
-    const bool no_ring = !(ring_env && std::atoi(ring_env) != 0);
-    std::vector<int32_t> lo_all, hi_all;
+    constexpr int kGroup = 8;
     std::vector<SweepBlock> blocks_all;
     h->sweep_ring_rows.assign(P, 0);
     h->window_offset.assign(P, 0);
-    h->ring_rows.assign(P, 0);
     for (int p = 0; p < P; ++p) {
       const PeriodTables &pt = h->tables.periods[p];
       const int G = (int)pt.grid.size(), groups = (G + kGroup - 1) / kGroup;
-      h->window_offset[p] = lo_all.size();
+      h->window_offset[p] = blocks_all.size();
       std::vector<int32_t> lo(groups, INT32_MAX), hi(groups, -1);
       for (int g = 0; g < G; ++g)
         for (int d2 = 0; d2 < pt.num_decisions[g]; ++d2) {
@@ -325,17 +318,6 @@ void build_device_tables(lsmc_handle *h) {
           lo[g / kGroup] = std::min(lo[g / kGroup], e.lower);
           hi[g / kGroup] = std::max(hi[g / kGroup], e.upper);
         }
-      bool ok = !no_ring;
-      int need = 0;
-      for (int j = 0; j < groups; ++j) {
-        if (j + 1 < groups && lo[j + 1] < lo[j]) ok = false;  // window must slide upwards
-        const int next_hi = j + 1 < groups ? std::max(hi[j + 1], hi[j]) : hi[j];
-        need = std::max(need, next_hi - lo[j] + 1);
-      }
-      if (need > kMaxRing) ok = false;
-      h->ring_rows[p] = ok ? std::max(need, 2) : 0;
-      lo_all.insert(lo_all.end(), lo.begin(), lo.end());
-      hi_all.insert(hi_all.end(), hi.begin(), hi.end());
       // Row-ring sweep kernel (backward_sweep.cu): while block j is evaluated the rows block j+1 adds are copied in, so
       // the ring must hold [lo(j), hi(j+1)] with hi a running maximum; usable when lo never decreases and the ring fits
       // beside the kernel's other shared-memory buffers with two CTAs per SM.
@@ -357,8 +339,6 @@ void build_device_tables(lsmc_handle *h) {
           blocks_all.push_back(SweepBlock{lo[j], hic[j], R ? lo[j] % R : 0, R ? hic[j] % R : 0});
       }
     }
-    h->win_lo.upload(lo_all);
-    h->win_hi.upload(hi_all);
     h->sweep_blocks.upload(blocks_all);
   }
 
@@ -511,7 +491,11 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   const int64_t num_tiles = (N + kTilePaths - 1) / kTilePaths;
   int sm_count = 148;
   cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device);
-  static const bool use_sweep = [] { const char *e = std::getenv("LSMC_SWEEP"); return !(e && e[0] == '0'); }();  // test hook
+  const bool time_steps = std::getenv("LSMC_NO_STEP_EVENTS") == nullptr;
+  const bool trace = std::getenv("LSMC_TRACE") != nullptr;
+  EventList tr(trace ? 5 * (size_t)(P + 1) : 0);
+  auto mark = [&](int p, int i) { if (trace) cudaEventRecord(tr[5 * (size_t)p + i], st); };
+  const bool use_sweep = [] { const char *e = std::getenv("LSMC_SWEEP"); return !(e && e[0] == '0'); }();  // test hook: 0 = general kernel
   auto q_buffer = [&](int period) { return h->qbuf[period % 3].ptr; };
   auto has_basis = [&](int period) { return period >= first_reg && period < P; };
   auto launch_basis_for = [&](int period) {
@@ -533,7 +517,9 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       if (e != cudaSuccess) throw CudaFailure(std::string("basis_kernel (period ") + std::to_string(period) + ") failed: " + cudaGetErrorString(e));
     }
   };
-  // The basis rows are independent of the value recursion, so they are produced on a second stream, three buffers deep:
+  // The basis rows are independent of the value recursion, so they are produced on a second stream, three buffers deep
+  // (equal stream priorities: measured, a low-priority basis stream ends up sharing the GPU with the sweep kernel and costs
+  // more than it hides; as it is, the basis kernel fills the SMs the small reduction and fold kernels leave idle):
   // step p reads q(p) and q(p-1); once it has finished, the buffer of q(p) is free for q(p-3), which is then computed while
   // step p-1 runs and is first needed by step p-2.
   cudaEventRecord(h->ev_prepass, st);
@@ -577,12 +563,11 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.q_prev = has_basis(p - 1) ? q_buffer(p - 1) : nullptr;
     a.partials = h->partials.ptr;
     // split the inventory grid over several CTAs only when there are too few path tiles to fill the GPU
-    const bool ring = !terminal && h->ring_rows[p] > 0;
-    const bool sweep = !terminal && !ring && D == 3 && use_sweep;
-    const int sub_size = (ring || sweep) ? 8 : kMaxGridTile;
+    const bool sweep = !terminal && D == 3 && use_sweep;
+    const int sub_size = sweep ? 8 : kMaxGridTile;
     const int subtiles = (a.G + sub_size - 1) / sub_size;
     const int64_t tiles = sweep ? (N + kSweepTilePaths - 1) / kSweepTilePaths : num_tiles;
-    const int64_t slots = (int64_t)sm_count * ((ring || sweep) ? 2 : 4);
+    const int64_t slots = (int64_t)sm_count * (sweep ? 3 : 4);
     int gsplit = (int)std::min<int64_t>(subtiles, std::max<int64_t>(1, (4 * slots + tiles - 1) / tiles));
     if (const char *forced = std::getenv("LSMC_GSPLIT")) gsplit = std::max(1, std::min(subtiles, std::atoi(forced)));  // test hook
     a.subtiles_per_cta = (subtiles + gsplit - 1) / gsplit;
@@ -602,26 +587,25 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       f.fused_payoff = a.fused_payoff;
       f.ring_rows = h->sweep_ring_rows[p];
       f.out = h->point_tables.ptr;
+      mark(p, 1);
       launch_fold_tables(f, st);
+      mark(p, 2);
       launches++;
       a.point_tables = h->point_tables.ptr;
       a.ring_rows = h->sweep_ring_rows[p];
       a.sweep_blocks = h->sweep_blocks.ptr + h->window_offset[p];
     }
-    if (!terminal) cudaEventRecord(step_events[2 * p], st);
-    if (ring) {
-      a.win_lo = h->win_lo.ptr + h->window_offset[p];
-      a.win_hi = h->win_hi.ptr + h->window_offset[p];
-      a.ring_rows = h->ring_rows[p];
-      launch_backward_ring(a, gsplit, num_tiles, st);
-    } else if (sweep) {
+    mark(p, 3);
+    if (!terminal && time_steps) cudaEventRecord(step_events[2 * p], st);
+    if (sweep) {
       launch_backward_sweep(a, gsplit, tiles, st);
     } else {
       launch_backward_step(a, gsplit, num_tiles, st);
     }
-    if (!terminal) cudaEventRecord(step_events[2 * p + 1], st);
+    if (!terminal && time_steps) cudaEventRecord(step_events[2 * p + 1], st);
+    mark(p, 4);
     launches++;
-    dbg(ring ? "backward_ring_kernel" : sweep ? "backward_sweep_kernel" : "backward_step_kernel", p);
+    dbg(sweep ? "backward_sweep_kernel" : "backward_step_kernel", p);
     if (has_basis(p - 3)) {
       cudaEventRecord(h->ev_step[p % 3], st);
       cudaStreamWaitEvent(h->aux_stream, h->ev_step[p % 3], 0);
@@ -661,11 +645,13 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   };
 
   double *v_next = h->v_a.ptr, *v_this = h->v_b.ptr;
+  const auto enqueue0 = std::chrono::steady_clock::now();
   int chunks = launch_step(P, true, nullptr, v_next);
   const double back_step = 0.66 / P;  // BackwardPcntTime (LSV.cs:48,164)
   double prog = 0.0;
   for (int p = P - 1; p >= 0; --p) {
     check_cancel();
+    mark(p, 0);
     reduce_gamma(p, (int)h->tables.periods[p + 1].grid.size(), chunks);
     chunks = launch_step(p, false, v_next, v_this);
     std::swap(v_next, v_this);
@@ -673,6 +659,18 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     if (progress) progress(prog, user);
   }
   const double *v_first = v_next;  // storage value by sim at period 0
+  if (trace) {
+    cudaStreamSynchronize(st);
+    for (int p = P / 2 + 2; p >= P / 2; --p) {
+      float m[5];
+      for (int i = 0; i < 5; ++i) cudaEventElapsedTime(&m[i], tr[5 * (size_t)(P / 2 + 2)], tr[5 * (size_t)p + i]);
+      std::fprintf(stderr, "[lsmc] step %d: start %.1f us | reduce done %.1f | fold done %.1f | sweep may start %.1f | sweep done %.1f\n", p,
+                   1e3 * m[0], 1e3 * m[1], 1e3 * m[2], 1e3 * m[3], 1e3 * m[4]);
+    }
+  }
+  if (trace)
+    std::fprintf(stderr, "[lsmc] backward induction: %d steps enqueued in %.3f ms of host time\n", P,
+                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - enqueue0).count());
   t_back.stop();
   check_cancel();
 
@@ -816,7 +814,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   h->scalars.ms_device = t_dev.ms();
   {
     double total = 0.0;
-    for (int p = 0; p < P; ++p) {
+    for (int p = 0; p < P && time_steps; ++p) {
       float m = 0.f;
       cudaEventElapsedTime(&m, step_events[2 * p], step_events[2 * p + 1]);
       total += m;

@@ -135,11 +135,15 @@ def test_larger_path_count_config1():
 
 
 @pytest.mark.parametrize("gsplit", ["1", "3"])
-def test_tma_ring_variant_of_backward_kernel(monkeypatch, gsplit):
-    """The opt-in backward kernel that stages the next period's value rows in a shared-memory ring with bulk TMA copies
-    (backward_ring.cu), with one CTA sweeping the whole grid (gsplit=1, exercises the double-buffered mbarriers) and with
-    the grid split over CTAs."""
-    monkeypatch.setenv("LSMC_RING", "1")
+@pytest.mark.parametrize("variant", ["row_ring", "direct_sweep", "general"])
+def test_backward_kernel_variants(monkeypatch, variant, gsplit):
+    """The three backward kernels against the oracle: the row-ring sweep kernel (default for three-decision tables whose row
+    windows slide upwards), the direct-load sweep kernel it falls back to, and the general kernel (any table width); each
+    with one CTA sweeping the whole grid of its path tile and with the grid split over several CTAs."""
+    if variant == "direct_sweep":
+        monkeypatch.setenv("LSMC_SWEEP_RING", "0")
+    elif variant == "general":
+        monkeypatch.setenv("LSMC_SWEEP", "0")
     monkeypatch.setenv("LSMC_GSPLIT", gsplit)
     check_case(cases.three_factor_ratchets(num_sims=1500, num_days=40, seed=13))
     check_case(cases.simple_one_factor(num_sims=1009, num_days=30, seed=6))
