@@ -321,7 +321,7 @@ def run_gpu(args):
            "config": workload_config(args, n, world),
            "evals_per_step": evals_total, "mean_grid_points": mean_grid, "npv": npv,
            "device_ms_per_step": device_ms / args.steps, "phases_last_step": phases, "setup_seconds_untimed": setup_s,
-           "roofline": {"bound": "hbm", "kernel": "backward_step_kernel<7>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+           "roofline": {"bound": "hbm", "kernel": "backward_sweep_ring_kernel<7,fused>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                         "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
                         "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": 1000.0 * avg_kernel_s,
                         "kernel_share_of_step": (kernel_ms / 1000.0 / args.steps) / step_s},
