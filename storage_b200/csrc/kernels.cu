@@ -59,6 +59,27 @@ __device__ __forceinline__ void eval_monomials(const BasisSpec &b, const int32_t
   for (int k = 0; k < KP; ++k) X[k] = (k < K) ? monomial_value(pw + k * (1 + F), F, s, x) : 0.0;
 }
 
+// The simulated inputs of one path (spot and factors of one period), loaded one loop iteration ahead of their use so the
+// global-load latency hides behind the previous path's arithmetic.
+struct PathInputs {
+  double s;
+  double x[LSMC_MAX_FACTORS];
+};
+__device__ __forceinline__ void load_inputs(const BasisSpec &b, int F, int64_t n, PathInputs &in) {
+  in.s = b.spot[n];
+#pragma unroll
+  for (int i = 0; i < LSMC_MAX_FACTORS; ++i)
+    if (i < F) in.x[i] = b.factors[i][n];
+}
+template <int KP>
+__device__ __forceinline__ void eval_monomials_from(const PathInputs &in, const int32_t *__restrict__ pw, int K, int F, double (&X)[KP]) {
+  double x[LSMC_MAX_FACTORS];
+#pragma unroll
+  for (int i = 0; i < LSMC_MAX_FACTORS; ++i) x[i] = (i < F) ? in.x[i] : 0.0;
+#pragma unroll
+  for (int k = 0; k < KP; ++k) X[k] = (k < K) ? monomial_value(pw + k * (1 + F), F, in.s, x) : 0.0;
+}
+
 // q_j = sum_{l<=j} X_l * (R.hi + R.lo)[l][j]: error-free products, cascaded (Dot2) summation, one final rounding
 template <int KP>
 __device__ __forceinline__ void orthonormalise(const double (&X)[KP], const dd *__restrict__ rinv, int K, double (&q)[KP]) {
@@ -153,9 +174,13 @@ __global__ void __launch_bounds__(kThreads) gram_kernel(GramArgs a) {
   for (int i = 0; i < NP; ++i) hi[i] = lo[i] = 0.0;
   const int64_t begin = (int64_t)blockIdx.x * a.chunk_paths;
   const int64_t end = min(begin + a.chunk_paths, a.N);
+  PathInputs next;
+  if (begin + threadIdx.x < end) load_inputs(b, F, begin + threadIdx.x, next);
   for (int64_t n = begin + threadIdx.x; n < end; n += blockDim.x) {
+    const PathInputs in = next;
+    if (n + blockDim.x < end) load_inputs(b, F, n + blockDim.x, next);
     double X[KP];
-    eval_monomials<KP>(b, s_pw, K, F, n, X);
+    eval_monomials_from<KP>(in, s_pw, K, F, X);
     int idx = 0;
 #pragma unroll
     for (int i = 0; i < KP; ++i)
@@ -722,26 +747,41 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
 #pragma unroll
     for (int k = 0; k < KP; ++k) qsum[k] = 0.0;
 
+    BasisSpec b;
+    b.mean_mode = pp.mean_mode;
+    b.rinv = nullptr;
+    b.spot = nullptr;
+    if (!pp.mean_mode) {
+      b.spot = a.spot + (size_t)pp.sim_row * a.sim_pitch;
+#pragma unroll
+      for (int i = 0; i < LSMC_MAX_FACTORS; ++i) b.factors[i] = (i < F) ? a.factors[i] + (size_t)pp.sim_row * a.sim_pitch : nullptr;
+    }
+    // the simulated inputs of the next tile are requested before the current tile's arithmetic
+    PathInputs next;
+    if (!pp.mean_mode && blockIdx.x < num_tiles) load_inputs(b, F, min((int64_t)blockIdx.x * kThreads + threadIdx.x, a.N - 1), next);
+
     for (int t = 0; t < a.tiles_per_cta; ++t) {
       const int64_t tile = blockIdx.x + (int64_t)t * gridDim.x;
       if (tile >= num_tiles) break;
       const int64_t n = tile * kThreads + threadIdx.x;
       const bool valid = n < a.N;
-      const int64_t nc = valid ? n : a.N - 1;
       double inventory = s_inv[t * kThreads + threadIdx.x];
-
-      BasisSpec b;
-      b.mean_mode = pp.mean_mode;
-      b.rinv = nullptr;
-      double price = pp.forward_price;
-      if (!pp.mean_mode) {
-        b.spot = a.spot + (size_t)pp.sim_row * a.sim_pitch;
-#pragma unroll
-        for (int i = 0; i < LSMC_MAX_FACTORS; ++i) b.factors[i] = (i < F) ? a.factors[i] + (size_t)pp.sim_row * a.sim_pitch : nullptr;
-        price = b.spot[nc];
-      }
+      const PathInputs in = next;
+      if (!pp.mean_mode && t + 1 < a.tiles_per_cta && tile + gridDim.x < num_tiles)
+        load_inputs(b, F, min((tile + gridDim.x) * kThreads + threadIdx.x, a.N - 1), next);
+      const double price = pp.mean_mode ? pp.forward_price : in.s;
       double q[KP];
-      eval_q<KP>(b, s_pw, s_rinv, K, F, nc, valid, q);
+#pragma unroll
+      for (int k = 0; k < KP; ++k) q[k] = 0.0;
+      if (valid) {
+        if (pp.mean_mode) {
+          q[0] = 1.0;
+        } else {
+          double X[KP];
+          eval_monomials_from<KP>(in, s_pw, K, F, X);
+          orthonormalise<KP>(X, s_rinv, K, q);
+        }
+      }
 
       // LSV.cs:445-508 for this path.  A breach of the inventory limits smaller than NumericalTolerance (rounding of
       // inv + v - loss after a constrained decision) is snapped onto the limit; the reference would throw (CS.cs:88-94).
