@@ -1423,6 +1423,81 @@ int oracle_period_grid(const lsmc_problem *pb, int period, double *out, int capa
   ORACLE_CATCH
 }
 
+// IntrinsicStorageValuation.Calculate (IntrinsicValuation/IntrinsicStorageValuation.cs:120-322) with the linear inventory-space
+// interpolator (InterpolatorFactories/LinearInterpolatorFactory.cs:36-49 -> MathNet LinearSpline, restated in linear_spline
+// above) and the fixed-spacing grid: deterministic dynamic programme on the forward curve.  It shares the inventory space,
+// grid, bang-bang decision set and MaxValueAndIndex helpers with the LSMC valuation, and the reference holds exact golden
+// values for it (src/Cmdty.Storage.Python/tests/test_multi_factor.py:102,123), which is what pins those helpers end to end.
+// profile is [P+1][5]: inventory after the decision, inject/withdraw volume, commodity consumed, inventory loss, period PV.
+int oracle_intrinsic_calculate(const lsmc_problem *pb, double *npv_out, double *profile) {
+  ORACLE_TRY
+  if (pb->inventory < 0) throw OracleError(LSMC_ERR_ARGUMENT, "Inventory cannot be negative.");  // :127-128
+  Storage st(pb->storage);
+  const int P = st.P;
+  const double tol = pb->numerical_tolerance;
+  if (P < 1) throw OracleError(LSMC_ERR_ARGUMENT, "Storage has expired");
+  std::vector<double> space_min(P + 1, 0.0), space_max(P + 1, 0.0);
+  calculate_inventory_space(st, pb->inventory, &space_min[1], &space_max[1]);  // :154
+
+  // value functions of periods 1..P as interpolation tables (period P: the terminal function, :188-190)
+  std::vector<std::vector<double>> grid(P + 1), value(P + 1);
+  auto continuation = [&](int period, double inventory) -> double {
+    if (period == P) return st.terminal_npv(pb->forward_price[P], inventory);
+    const std::vector<double> &x = grid[period], &y = value[period];
+    if (x.size() == 1) return y[0];  // LinearInterpolatorFactory.cs:43-47
+    return linear_spline(x.data(), y.data(), (int)x.size(), inventory);
+  };
+  struct Decision {
+    double storage_npv, inject_withdraw, consumed, loss, period_pv;
+  };
+  // OptimalDecisionAndValue (:260-291) + StorageValueForDecision (:294-322)
+  auto optimal = [&](int p, double inventory) -> Decision {
+    const Range range = st.inject_withdraw_range(p, inventory);
+    const double loss = st.loss_pct(p) * inventory;
+    const std::vector<double> decisions = bang_bang_decision_set(range, inventory, loss, space_min[p + 1], space_max[p + 1], tol, 0);
+    const double price = pb->forward_price[p], df = pb->settle_df[p];
+    std::vector<double> values(decisions.size()), consumed(decisions.size()), pvs(decisions.size());
+    for (size_t j = 0; j < decisions.size(); j++) {
+      const double v = decisions[j];
+      const double after = inventory + v - loss;
+      const double cont = continuation(p + 1, after);
+      const double inject_withdraw_npv = -v * price * df;
+      const double inventory_cost_npv = st.inventory_cost_npv(p, inventory);
+      const double decision_cost_npv = st.inject_withdraw_cost_npv(p, v);
+      const double used = st.cmdty_consumed(p, v);
+      const double used_npv = -used * price * df;
+      const double period_pv = inject_withdraw_npv - decision_cost_npv + used_npv - inventory_cost_npv;
+      values[j] = cont + period_pv;
+      consumed[j] = used;
+      pvs[j] = period_pv;
+    }
+    double best;
+    const int idx = max_value_and_index(values.data(), (int)values.size(), &best);
+    return {best, decisions[idx], consumed[idx], loss, pvs[idx]};
+  };
+  for (int p = P - 1; p >= 1; p--) {  // :196-223
+    grid[p] = grid_points(space_min[p], space_max[p], pb->grid_spacing);
+    value[p].resize(grid[p].size());
+    for (size_t i = 0; i < grid[p].size(); i++) value[p][i] = optimal(p, grid[p][i]).storage_npv;
+  }
+  // forward from the starting inventory (:225-255)
+  double inventory = pb->inventory, npv = 0.0;
+  for (int p = 0; p <= P; p++) {
+    double *row = profile + (size_t)p * 5;
+    if (p == P) {
+      const double end_npv = pb->storage.must_be_empty_at_end ? 0.0 : st.terminal_npv(pb->forward_price[P], inventory);
+      row[0] = inventory, row[1] = 0.0, row[2] = 0.0, row[3] = 0.0, row[4] = end_npv;
+    } else {
+      const Decision d = optimal(p, inventory);
+      inventory += d.inject_withdraw - d.loss;
+      row[0] = inventory, row[1] = d.inject_withdraw, row[2] = d.consumed, row[3] = d.loss, row[4] = d.period_pv;
+    }
+    npv += row[4];  // storageProfiles.Sum(profile => profile.PeriodPv), :257
+  }
+  *npv_out = npv;
+  ORACLE_CATCH
+}
+
 int oracle_num_threads() {
 #ifdef _OPENMP
   return omp_get_max_threads();

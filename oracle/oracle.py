@@ -161,5 +161,14 @@ def lsmc_calculate(flat, reg_spot, reg_factors, val_spot, val_factors, mode=1, t
     return out
 
 
+def intrinsic_calculate(flat):
+    """oracle_intrinsic_calculate on a storage_b200.FlatProblem: (npv, profile[P+1][5])."""
+    P = flat.num_periods
+    npv = C.c_double()
+    profile = np.zeros((P + 1, 5))
+    _check(lib().oracle_intrinsic_calculate(C.byref(flat.struct), C.byref(npv), _dp(profile)))
+    return npv.value, profile
+
+
 def num_threads():
     return lib().oracle_num_threads()
