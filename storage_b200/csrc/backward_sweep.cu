@@ -413,6 +413,37 @@ __device__ __forceinline__ void evaluate4_ring(const PointTable<KC> *__restrict_
   }
 }
 
+// Bulk asynchronous copies (the TMA engine's 1-D form) complete on an mbarrier by byte count: one instruction moves a whole
+// 1 KB row or a whole sub-tile of point records, no thread holds registers for it and nothing crosses the LSU data pipe.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
+
 template <int KP, bool FUSED>
 __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_sweep_ring_kernel(BackwardStepArgs a) {
   constexpr int KC = (KP + 1) & ~1;
@@ -426,7 +457,6 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   double *s_acc = s_v + 2 * kBlockG * kVPitch;                               // [2][kRingWarps][ACC][kBlockG]
   char *s_rows = reinterpret_cast<char *>(s_acc + 2 * kRingWarps * ACC * kBlockG);  // [R][kRowBytes]
   const int R = a.ring_rows;
-  SweepBlock *s_blk = reinterpret_cast<SweepBlock *>(s_rows + (size_t)R * kRowBytes);  // [a.subtiles_per_cta]
 
   const int K = a.K;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;  // warp = grid slot
@@ -449,48 +479,50 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   const int glimit = min(a.G, (bbeg + nblocks) * kBlockG) - gbeg;
 
   const Table *tab = reinterpret_cast<const Table *>(a.point_tables) + gbeg;
-  auto stage = [&](int sub) {
-    const int first = sub * kRingTabSub;
-    const int count = min(kRingTabSub, glimit - first);
-    if (count <= 0) return;
-    const char *src = reinterpret_cast<const char *>(tab + first);
-    char *dst = reinterpret_cast<char *>(s_tab + (sub & 1) * kRingTabSub);
-    const int chunks = count * (int)(sizeof(Table) / 16);
-#pragma unroll 1
-    for (int i = threadIdx.x; i < chunks; i += kRingThreads) cp_async_16(dst + 16 * i, src + 16 * i);
-  };
-  // rows [first_row, first_row + count) of this tile's 128 columns into ring slots first_slot.. (mod R): one warp per row,
-  // two 16-byte pieces per lane
   const uint32_t pitch_bytes = (uint32_t)a.pitch * 8u;
-  const char *tile_rows = reinterpret_cast<const char *>(a.v_next + tile * kSweepTilePaths) + lane * 16;
-  char *ring_dst = s_rows + lane * 16;
-  auto fetch_rows = [&](int first_row, int first_slot, int count) {
+  const char *tile_rows = reinterpret_cast<const char *>(a.v_next + tile * kSweepTilePaths);
+  const SweepBlock *blk = a.sweep_blocks + bbeg;
+  __shared__ __align__(8) uint64_t s_mbar[2];
+
+  // Generation j = everything block j needs that is not resident yet: the rows its window adds to the ring and, every other
+  // block, the next sub-tile of point records.  One elected thread posts the byte count on mbarrier j & 1 and issues the bulk
+  // copies; everybody waits on that barrier's phase (j >> 1) & 1 before starting block j.
+  auto issue_generation = [&](int j) {  // one thread only
+    uint64_t *bar = &s_mbar[j & 1];
+    int first_row, first_slot, count;
+    if (j == 0) {
+      first_row = blk[0].lo, first_slot = blk[0].lo_slot, count = blk[0].hi - blk[0].lo + 1;
+    } else {
+      const SweepBlock cur = blk[j - 1], nxt = blk[j];
+      first_row = cur.hi + 1, first_slot = cur.hi_slot + 1, count = nxt.hi - cur.hi;
+    }
+    const int sub = j >> 1;  // records of sub-tile `sub` travel with its first block's generation, one block ahead of its use
+    const int rec_first = sub * kRingTabSub;
+    const int rec_count = (j & 1) == 0 ? max(0, min(kRingTabSub, glimit - rec_first)) : 0;
+    mbar_expect_tx(bar, (uint32_t)count * kRowBytes + (uint32_t)rec_count * (uint32_t)sizeof(Table));
+    if (rec_count > 0) bulk_load(s_tab + (sub & 1) * kRingTabSub, tab + rec_first, (uint32_t)rec_count * (uint32_t)sizeof(Table), bar);
 #pragma unroll 1
-    for (int j = warp; j < count; j += kRingWarps) {
-      int s = first_slot + j;
-      if (s >= R) s -= R;
-      const char *src = row_address(tile_rows, (uint32_t)(first_row + j), pitch_bytes);
-      char *dst = ring_dst + s * kRowBytes;
-      cp_async_16(dst, src);
-      cp_async_16(dst + 512, src + 512);
+    for (int i = 0; i < count; ++i) {
+      int slot_i = first_slot + i;
+      if (slot_i >= R) slot_i -= R;
+      bulk_load(s_rows + (size_t)slot_i * kRowBytes, row_address(tile_rows, (uint32_t)(first_row + i), pitch_bytes), kRowBytes, bar);
+    }
+    if (j + 2 < nblocks) {  // ask L2 for the rows two generations further on
+      const int pf_first = blk[j + 1].hi + 1, pf_count = blk[j + 2].hi - blk[j + 1].hi;
+#pragma unroll 1
+      for (int i = 0; i < pf_count; ++i) bulk_prefetch_l2(row_address(tile_rows, (uint32_t)(pf_first + i), pitch_bytes), kRowBytes);
     }
   };
-  auto request_rows = [&](int first_row, int count) {  // into L2 only: one 128-byte line per lane, lanes 0..7
-    if (lane < 8)
-#pragma unroll 1
-      for (int j = warp; j < count; j += kRingWarps)
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(row_address(tile_rows, (uint32_t)(first_row + j), pitch_bytes) + lane * 112));
-  };
-
-  const SweepBlock *blk = a.sweep_blocks + bbeg;
-  stage(0);
-  {
-    const SweepBlock w = blk[0];
-    fetch_rows(w.lo, w.lo_slot, w.hi - w.lo + 1);
-    if (nblocks > 1) request_rows(w.hi + 1, blk[1].hi - w.hi);
-    if (nblocks > 2) request_rows(blk[1].hi + 1, blk[2].hi - blk[1].hi);
+  if (threadIdx.x == 0) {
+    mbar_init(&s_mbar[0], 1);
+    mbar_init(&s_mbar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (int i = threadIdx.x; i < nblocks; i += kRingThreads) s_blk[i] = blk[i];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    issue_generation(0);
+    if (nblocks > 1) issue_generation(1);  // its records are the second sub-tile only from block 2 on: (1 & 1) != 0, rows only
+  }
 
   double price[kLanePaths];
 #pragma unroll
@@ -554,17 +586,12 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
     }
   };
 
-  cp_async_wait_all();
-  __syncthreads();
+  mbar_wait(&s_mbar[0], 0);
 
   for (int b = 0; b < nblocks; ++b) {
-    // every warp has finished block b-1: its table half and the ring slots below this block's window are free
-    if ((b & 1) == 0) stage((b >> 1) + 1);
-    if (b + 1 < nblocks) {
-      const SweepBlock cur = s_blk[b], nxt = s_blk[b + 1];
-      fetch_rows(cur.hi + 1, cur.hi_slot + 1, nxt.hi - cur.hi);
-      if (b + 3 < nblocks) request_rows(s_blk[b + 2].hi + 1, s_blk[b + 3].hi - s_blk[b + 2].hi);
-    }
+    // every warp has finished block b-1 (barrier at the end of the previous iteration): the record half and the ring slots
+    // that generation b+1 overwrites are free.  Generation 1 was issued in the prologue.
+    if (b > 0 && b + 1 < nblocks && threadIdx.x == 32 * (b & 3)) issue_generation(b + 1);
     const int gA = b * kBlockG + warp, gB = gA + kSlots;
     const Table *tA = s_tab + (min(gA, last) & (kRingTabRing - 1));
     const Table *tB = s_tab + (min(gB, last) & (kRingTabRing - 1));
@@ -589,8 +616,8 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
       *reinterpret_cast<double2 *>(vt + kSlots * kVPitch) = make_double2(vB[0], vB[1]);
       *reinterpret_cast<double2 *>(vt + kSlots * kVPitch + kPairGap) = make_double2(vB[2], vB[3]);
     }
-    cp_async_wait_all();  // this thread's share of the next block's rows (and table records) has landed ...
-    __syncthreads();      // ... and so has everybody else's
+    if (b + 1 < nblocks) mbar_wait(&s_mbar[(b + 1) & 1], ((b + 1) >> 1) & 1);  // rows and records of the next block have landed
+    __syncthreads();  // the regression tile is complete; nobody still reads what the next generation overwrites
     if (a.accumulate) {
       // C[k][g] = sum over the warp's 32 paths of q_prev[k][n] * V[g][n]; C fragment: row -> k, columns 2 col + {0,1} -> g
       const double *vb = my_b + buf * (kBlockG * kVPitch);
@@ -663,7 +690,7 @@ size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta) 
   const int KP = padded_basis(K);
   const int ACC = KP <= 8 ? 8 : 16;
   return point_table_bytes(K) * kRingTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kRingWarps * kBlockG * ACC) +
-         (size_t)ring_rows * kRowBytes + (size_t)blocks_per_cta * sizeof(SweepBlock);
+         (size_t)ring_rows * kRowBytes;
 }
 
 void launch_fold_tables(const FoldArgs &f, cudaStream_t stream) {
