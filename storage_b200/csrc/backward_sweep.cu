@@ -595,27 +595,34 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
     const int gA = b * kBlockG + warp, gB = gA + kSlots;
     const Table *tA = s_tab + (min(gA, last) & (kRingTabRing - 1));
     const Table *tB = s_tab + (min(gB, last) & (kRingTabRing - 1));
-    double vA[kLanePaths], vB[kLanePaths];
-    evaluate4_ring<KP, KC, FUSED>(tA, my_rows, q, price, df, vA);
-    evaluate4_ring<KP, KC, FUSED>(tB, my_rows, q, price, df, vB);
-    if (gA <= last) {
-      if (validA) *reinterpret_cast<double2 *>(vout) = make_double2(vA[0], vA[1]);
-      if (validB) *reinterpret_cast<double2 *>(vout + kPairGap * 8) = make_double2(vA[2], vA[3]);
+    const int buf = b & 1;
+    double *vt = my_v + buf * (kBlockG * kVPitch);
+    {  // first point: evaluate, store, publish to the regression tile (its registers are free before the second point starts)
+      double v[kLanePaths];
+      evaluate4_ring<KP, KC, FUSED>(tA, my_rows, q, price, df, v);
+      if (gA <= last) {
+        if (validA) *reinterpret_cast<double2 *>(vout) = make_double2(v[0], v[1]);
+        if (validB) *reinterpret_cast<double2 *>(vout + kPairGap * 8) = make_double2(v[2], v[3]);
+      }
+      if (a.accumulate) {
+        *reinterpret_cast<double2 *>(vt) = make_double2(v[0], v[1]);
+        *reinterpret_cast<double2 *>(vt + kPairGap) = make_double2(v[2], v[3]);
+      }
     }
-    if (gB <= last) {
-      char *vo = vout + (uint64_t)kSlots * pitch_bytes;
-      if (validA) *reinterpret_cast<double2 *>(vo) = make_double2(vB[0], vB[1]);
-      if (validB) *reinterpret_cast<double2 *>(vo + kPairGap * 8) = make_double2(vB[2], vB[3]);
+    {  // second point
+      double v[kLanePaths];
+      evaluate4_ring<KP, KC, FUSED>(tB, my_rows, q, price, df, v);
+      if (gB <= last) {
+        char *vo = vout + (uint64_t)kSlots * pitch_bytes;
+        if (validA) *reinterpret_cast<double2 *>(vo) = make_double2(v[0], v[1]);
+        if (validB) *reinterpret_cast<double2 *>(vo + kPairGap * 8) = make_double2(v[2], v[3]);
+      }
+      if (a.accumulate) {
+        *reinterpret_cast<double2 *>(vt + kSlots * kVPitch) = make_double2(v[0], v[1]);
+        *reinterpret_cast<double2 *>(vt + kSlots * kVPitch + kPairGap) = make_double2(v[2], v[3]);
+      }
     }
     vout += (uint64_t)kBlockG * pitch_bytes;
-    const int buf = b & 1;
-    if (a.accumulate) {
-      double *vt = my_v + buf * (kBlockG * kVPitch);
-      *reinterpret_cast<double2 *>(vt) = make_double2(vA[0], vA[1]);
-      *reinterpret_cast<double2 *>(vt + kPairGap) = make_double2(vA[2], vA[3]);
-      *reinterpret_cast<double2 *>(vt + kSlots * kVPitch) = make_double2(vB[0], vB[1]);
-      *reinterpret_cast<double2 *>(vt + kSlots * kVPitch + kPairGap) = make_double2(vB[2], vB[3]);
-    }
     if (b + 1 < nblocks) mbar_wait(&s_mbar[(b + 1) & 1], ((b + 1) >> 1) & 1);  // rows and records of the next block have landed
     __syncthreads();  // the regression tile is complete; nobody still reads what the next generation overwrites
     if (a.accumulate) {
