@@ -36,27 +36,28 @@ constexpr unsigned kFullMask = 0xffffffffu;
 // compensated (twice-the-working-precision) summation.  Loops over factors are deliberately not unrolled: this code is
 // cold relative to the decision loop and must stay small in the instruction cache.
 // ------------------------------------------------------------------------------------------------------------------
-__device__ __noinline__ double monomial_value(const int32_t *__restrict__ row, int F, double s, const double *__restrict__ x) {
-  double m = 1.0;
-  const int p0 = row[0];
-  if (p0 > 0) m = pow_int_rounded(s, p0);
-#pragma unroll 1
-  for (int i = 0; i < F; ++i) {
-    const int pi = row[1 + i];
-    if (pi > 0) m = m * pow_int_rounded(x[i], pi);
+// The exponent table compiled into a term list once per CTA: monomial k is the product of var[t]^pow[t] for
+// t in [begin[k], begin[k+1]), spot first, then factors in index order (only the non-zero exponents).
+constexpr int kMaxTerms = LSMC_MAX_BASIS * (1 + LSMC_MAX_FACTORS);
+struct MonomialProgram {
+  int32_t begin[LSMC_MAX_BASIS + 1];
+  int8_t var[kMaxTerms];
+  int8_t pow[kMaxTerms];
+};
+__device__ __forceinline__ void build_monomial_program(MonomialProgram &pr, const int32_t *__restrict__ pw, int K, int F) {  // one thread
+  int n = 0;
+  for (int k = 0; k < K; ++k) {
+    pr.begin[k] = n;
+    for (int v = 0; v <= F; ++v) {
+      const int p = pw[k * (1 + F) + v];
+      if (p > 0) {
+        pr.var[n] = (int8_t)v;
+        pr.pow[n] = (int8_t)p;
+        ++n;
+      }
+    }
   }
-  return m;
-}
-
-template <int KP>
-__device__ __forceinline__ void eval_monomials(const BasisSpec &b, const int32_t *__restrict__ pw, int K, int F, int64_t n,
-                                               double (&X)[KP]) {
-  const double s = b.spot[n];
-  double x[LSMC_MAX_FACTORS];
-#pragma unroll 1
-  for (int i = 0; i < F; ++i) x[i] = b.factors[i][n];
-#pragma unroll
-  for (int k = 0; k < KP; ++k) X[k] = (k < K) ? monomial_value(pw + k * (1 + F), F, s, x) : 0.0;
+  for (int k = K; k <= LSMC_MAX_BASIS; ++k) pr.begin[k] = n;
 }
 
 // The simulated inputs of one path (spot and factors of one period), loaded one loop iteration ahead of their use so the
@@ -72,12 +73,22 @@ __device__ __forceinline__ void load_inputs(const BasisSpec &b, int F, int64_t n
     if (i < F) in.x[i] = b.factors[i][n];
 }
 template <int KP>
-__device__ __forceinline__ void eval_monomials_from(const PathInputs &in, const int32_t *__restrict__ pw, int K, int F, double (&X)[KP]) {
-  double x[LSMC_MAX_FACTORS];
+__device__ __forceinline__ void eval_monomials_from(const PathInputs &in, const MonomialProgram &pr, int K, int F, double (&X)[KP]) {
+  double v[1 + LSMC_MAX_FACTORS];  // indexed by the program: lives in local memory (L1)
+  v[0] = in.s;
 #pragma unroll
-  for (int i = 0; i < LSMC_MAX_FACTORS; ++i) x[i] = (i < F) ? in.x[i] : 0.0;
+  for (int i = 0; i < LSMC_MAX_FACTORS; ++i)
+    if (i < F) v[1 + i] = in.x[i];
 #pragma unroll
-  for (int k = 0; k < KP; ++k) X[k] = (k < K) ? monomial_value(pw + k * (1 + F), F, in.s, x) : 0.0;
+  for (int k = 0; k < KP; ++k) {
+    double m = 1.0;  // 1.0 * x is exact: the first factor enters unrounded, as in the reference's product
+    if (k < K) {
+      const int end = pr.begin[k + 1];
+#pragma unroll 1
+      for (int t = pr.begin[k]; t < end; ++t) m = m * pow_int_rounded(v[pr.var[t]], pr.pow[t]);
+    }
+    X[k] = (k < K) ? m : 0.0;
+  }
 }
 
 // q_j = sum_{l<=j} X_l * (R.hi + R.lo)[l][j]: error-free products, cascaded (Dot2) summation, one final rounding
@@ -103,7 +114,7 @@ __device__ __forceinline__ void orthonormalise(const double (&X)[KP], const dd *
 }
 
 template <int KP>
-__device__ __forceinline__ void eval_q(const BasisSpec &b, const int32_t *__restrict__ pw, const dd *__restrict__ rinv, int K,
+__device__ __forceinline__ void eval_q(const BasisSpec &b, const MonomialProgram &pr, const dd *__restrict__ rinv, int K,
                                        int F, int64_t n, bool valid, double (&q)[KP]) {
 #pragma unroll
   for (int k = 0; k < KP; ++k) q[k] = 0.0;
@@ -113,7 +124,9 @@ __device__ __forceinline__ void eval_q(const BasisSpec &b, const int32_t *__rest
     return;
   }
   double X[KP];
-  eval_monomials<KP>(b, pw, K, F, n, X);
+  PathInputs in;
+  load_inputs(b, F, n, in);
+  eval_monomials_from<KP>(in, pr, K, F, X);
   orthonormalise<KP>(X, rinv, K, q);
 }
 
@@ -166,7 +179,10 @@ __global__ void __launch_bounds__(kThreads) gram_kernel(GramArgs a) {
   const int slot = blockIdx.y;
   const BasisSpec b = a.specs[slot];
   const int K = a.K, F = a.F;
+  __shared__ MonomialProgram s_prog;
   for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
+  __syncthreads();
+  if (threadIdx.x == 0) build_monomial_program(s_prog, s_pw, K, F);
   __syncthreads();
   // compensated accumulation: hi carries the running sum, lo collects the rounding errors of the sums and products
   double hi[NP], lo[NP];
@@ -180,7 +196,7 @@ __global__ void __launch_bounds__(kThreads) gram_kernel(GramArgs a) {
     const PathInputs in = next;
     if (n + blockDim.x < end) load_inputs(b, F, n + blockDim.x, next);
     double X[KP];
-    eval_monomials_from<KP>(in, s_pw, K, F, X);
+    eval_monomials_from<KP>(in, s_prog, K, F, X);
     int idx = 0;
 #pragma unroll
     for (int i = 0; i < KP; ++i)
@@ -285,8 +301,11 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
   __shared__ int32_t s_pw[LSMC_MAX_BASIS * (1 + LSMC_MAX_FACTORS)];
   __shared__ dd s_rinv[LSMC_MAX_BASIS * LSMC_MAX_BASIS];
   const int K = a.K, F = a.F;
+  __shared__ MonomialProgram s_prog;
   for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
   for (int i = threadIdx.x; i < K * K; i += blockDim.x) s_rinv[i] = dd{a.spec.rinv[2 * i], a.spec.rinv[2 * i + 1]};
+  __syncthreads();
+  if (threadIdx.x == 0) build_monomial_program(s_prog, s_pw, K, F);
   __syncthreads();
   const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= a.N) {  // padding columns of the rows stay zero: the backward kernels load them as the odd half of a double2
@@ -295,7 +314,7 @@ __global__ void __launch_bounds__(256) basis_kernel(BasisArgs a) {
     return;
   }
   double q[KP];
-  eval_q<KP>(a.spec, s_pw, s_rinv, K, F, n, true, q);
+  eval_q<KP>(a.spec, s_prog, s_rinv, K, F, n, true, q);
 #pragma unroll
   for (int k = 0; k < KP; ++k)
     if (k < K) a.q_out[(size_t)k * a.pitch + n] = q[k];
@@ -720,7 +739,10 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
   __shared__ DevPeriodParams s_pp;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __shared__ MonomialProgram s_prog;
   for (int i = threadIdx.x; i < K * (1 + F); i += blockDim.x) s_pw[i] = a.powers[i];
+  __syncthreads();
+  if (threadIdx.x == 0) build_monomial_program(s_prog, s_pw, K, F);
 
   // A CTA owns tiles blockIdx.x, blockIdx.x + gridDim.x, ... (at most a.tiles_per_cta of them).  Periods are the outer loop so
   // that the period's tables (regression coefficients, next grid, R^-1) are staged once per CTA and period; the state a path
@@ -781,7 +803,7 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
           q[0] = 1.0;
         } else {
           double X[KP];
-          eval_monomials_from<KP>(in, s_pw, K, F, X);
+          eval_monomials_from<KP>(in, s_prog, K, F, X);
           orthonormalise<KP>(X, s_rinv, K, q);
         }
       }
