@@ -95,6 +95,7 @@ struct ForwardArgs {
   const double *factors[LSMC_MAX_FACTORS];
   double start_inventory;
   double tolerance;
+  double inv_grid_spacing;         // 1 / spacing of the fixed-spacing inventory grids
   int extra_decisions;
   double *pv_by_sim;               // [N]
   double *final_inventory;         // [N]

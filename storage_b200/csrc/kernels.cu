@@ -689,7 +689,7 @@ __device__ __forceinline__ int decision_set_dev(DevRange r, double inventory, do
 }
 
 // StorageHelper.BisectInventorySpace (SH.cs:280-314)
-__device__ __forceinline__ void bisect_dev(const double *grid, int n, double inventory, double tol, int *lower, int *upper, int *err) {
+__device__ __noinline__ void bisect_dev(const double *grid, int n, double inventory, double tol, int *lower, int *upper, int *err) {
   if (n == 1 && fabs(inventory - grid[0]) <= tol) {
     *lower = *upper = 0;
     return;
@@ -722,6 +722,28 @@ __device__ __forceinline__ void bisect_dev(const double *grid, int n, double inv
   }
   *err = LSMC_ERR_ARGUMENT;
   *lower = *upper = (inventory < grid[0]) ? 0 : n - 1;  // keep running on the nearest point; the flag fails the run
+}
+
+// The same result without the search when it cannot depend on the search path: on the fixed-spacing grid the bracketing
+// interval is computed directly, and if the inventory is further than the tolerance from both of its end points the
+// reference's bisection returns exactly that bracket whatever mid-points it visits.  Grid hits, tolerance cases and
+// out-of-range inventories go through the reference's search.
+__device__ __forceinline__ void bracket_dev(const double *grid, int n, double inventory, double tol, double inv_spacing, int *lower,
+                                            int *upper, int *err) {
+  if (n >= 2) {
+    int i = (int)((inventory - grid[0]) * inv_spacing);
+    i = max(0, min(i, n - 2));
+    if (inventory < grid[i] && i > 0)
+      --i;
+    else if (inventory > grid[i + 1] && i < n - 2)
+      ++i;
+    if (inventory - grid[i] > tol && grid[i + 1] - inventory > tol) {
+      *lower = i;
+      *upper = i + 1;
+      return;
+    }
+  }
+  bisect_dev(grid, n, inventory, tol, lower, upper, err);
 }
 
 template <int KP>
@@ -829,7 +851,7 @@ __global__ void __launch_bounds__(kThreads) forward_kernel(ForwardArgs a) {
         const double cost_npv = volume > 0.0 ? (pp.inj_cost * volume) * pp.inj_df : (pp.wd_cost * fabs(-volume)) * pp.wd_df;
         const double immediate = ((inject_withdraw_npv - cost_npv) + consumed_npv) - inv_cost_npv;  // LSV.cs:473
         int lo, hi;
-        bisect_dev(s_grid, Gn, after, a.tolerance, &lo, &hi, &err);
+        bracket_dev(s_grid, Gn, after, a.tolerance, a.inv_grid_spacing, &lo, &hi, &err);
         const double *gl = s_gamma + (size_t)lo * K;
         double c_lo = q[0] * gl[0];
 #pragma unroll

@@ -703,6 +703,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   for (int i = 0; i < F; ++i) fa.factors[i] = h->sims[1].factors[i];
   fa.start_inventory = h->inventory;
   fa.tolerance = h->tolerance;
+  fa.inv_grid_spacing = 1.0 / h->grid_spacing;
   fa.extra_decisions = h->extra;
   fa.pv_by_sim = h->pv.ptr;
   fa.final_inventory = h->final_inv.ptr;
