@@ -86,6 +86,7 @@ struct ForwardArgs {
   int64_t sim_pitch;               // N (caller layout)
   const DevPeriodParams *periods;  // [P]
   const double *ratchet_inventory, *ratchet_min, *ratchet_max;
+  const double *ratchet_min_slope, *ratchet_max_slope;  // per ratchet segment: (y[k+1]-y[k]) / (x[k+1]-x[k]) (piecewise-linear kind)
   const double *poly_min, *poly_max;
   const double *grids;             // [P+1][Gmax]
   const double *gamma;             // [P][Gmax][K]

@@ -641,8 +641,14 @@ __device__ __forceinline__ DevRange storage_range_dev(const ForwardArgs &a, cons
   switch (pp.kind) {
     case LSMC_CONSTRAINT_CONSTANT:
       return {mn[0], mx[0]};
-    case LSMC_CONSTRAINT_PIECEWISE_LINEAR:
-      return {spline_dev(xi, mn, pp.rcount, inventory), spline_dev(xi, mx, pp.rcount, inventory)};
+    case LSMC_CONSTRAINT_PIECEWISE_LINEAR: {
+      // MathNet LinearSpline: y_k + (t - x_k) * slope_k with the slopes formed once (host, same division), one segment
+      // search for both splines
+      int k = left_segment_dev(xi, pp.rcount, inventory);
+      k = max(0, min(k, pp.rcount - 2));
+      const double dx = inventory - xi[k];
+      return {mn[k] + dx * a.ratchet_min_slope[pp.rbegin + k], mx[k] + dx * a.ratchet_max_slope[pp.rbegin + k]};
+    }
     case LSMC_CONSTRAINT_STEP: {
       if (inventory < xi[0] || inventory > xi[pp.rcount - 1]) *err = LSMC_ERR_ARGUMENT;
       int idx = max(0, min(left_segment_dev(xi, pp.rcount, inventory), pp.rcount - 1));

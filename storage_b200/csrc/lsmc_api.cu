@@ -98,7 +98,7 @@ struct lsmc_handle {
   cudaEvent_t ev_basis[3] = {}, ev_step[3] = {}, ev_prepass = nullptr;
   SimSet sims[2];
   DeviceBuffer<double> v_a, v_b, grids, gamma, rinv, partials, gram_partials, inv_cost, pv, final_inv, step_sums, step_totals,
-      block_sums, gather_buf, qbuf[3], ratchet_inv, ratchet_min, ratchet_max, poly_min, poly_max;
+      block_sums, gather_buf, qbuf[3], ratchet_inv, ratchet_min, ratchet_max, ratchet_min_slope, ratchet_max_slope, poly_min, poly_max;
   DeviceBuffer<DevDecision> decisions;
   DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
@@ -379,6 +379,18 @@ void build_device_tables(lsmc_handle *h) {
   h->ratchet_inv.upload(st.r_inv_);
   h->ratchet_min.upload(st.r_min_);
   h->ratchet_max.upload(st.r_max_);
+  {  // spline slopes per ratchet segment (the last knot of a period has none)
+    std::vector<double> smin(st.r_inv_.size(), 0.0), smax(st.r_inv_.size(), 0.0);
+    for (int p = 0; p < P; ++p)
+      for (int k = 0; k + 1 < st.rcount_[p]; ++k) {
+        const size_t i = (size_t)st.rbegin_[p] + k;
+        const double dx = st.r_inv_[i + 1] - st.r_inv_[i];
+        smin[i] = (st.r_min_[i + 1] - st.r_min_[i]) / dx;
+        smax[i] = (st.r_max_[i + 1] - st.r_max_[i]) / dx;
+      }
+    h->ratchet_min_slope.upload(smin);
+    h->ratchet_max_slope.upload(smax);
+  }
   h->poly_min.upload(st.poly_min_);
   h->poly_max.upload(st.poly_max_);
   h->d_powers.upload(h->powers);
@@ -693,6 +705,8 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.ratchet_inventory = h->ratchet_inv.ptr;
   fa.ratchet_min = h->ratchet_min.ptr;
   fa.ratchet_max = h->ratchet_max.ptr;
+  fa.ratchet_min_slope = h->ratchet_min_slope.ptr;
+  fa.ratchet_max_slope = h->ratchet_max_slope.ptr;
   fa.poly_min = h->poly_min.ptr;
   fa.poly_max = h->poly_max.ptr;
   fa.grids = h->grids.ptr;
