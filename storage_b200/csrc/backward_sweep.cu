@@ -24,6 +24,7 @@
 #include "backward_common.cuh"
 #include "device_types.hpp"
 #include "kernels.hpp"
+#include "reduce_partials.cuh"
 
 #ifndef LSMC_SWEEP_PF
 #define LSMC_SWEEP_PF 8  // rows ahead of the window that are requested into L2
@@ -66,9 +67,7 @@ __device__ __forceinline__ void cp_async_16(void *dst_smem, const void *src) {
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 template <int KC>
-__global__ void fold_tables_kernel(FoldArgs f) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= f.G * 3) return;
+__device__ __forceinline__ void fold_item(const FoldArgs &f, int i) {  // i = 3 g + d
   const int g = i / 3, d = i - 3 * g;
   PointTable<KC> *t = reinterpret_cast<PointTable<KC> *>(f.out) + g;
   const int nd = f.num_decisions[g];
@@ -88,7 +87,37 @@ __global__ void fold_tables_kernel(FoldArgs f) {
   // direct-load kernel: row indices; row-ring kernel: byte offsets of the rows' slots in the shared-memory ring
   t->lower_row[d] = f.ring_rows > 0 ? (uint32_t)(e.lower % f.ring_rows) * (uint32_t)(kSweepTilePaths * 8) : (uint32_t)e.lower;
   t->upper_row[d] = f.ring_rows > 0 ? (uint32_t)(e.upper % f.ring_rows) * (uint32_t)(kSweepTilePaths * 8) : (uint32_t)e.upper;
-  fold_coefficients<KC>(e, f.gamma, f.K, t->c[d]);
+  // gamma may have been written by other CTAs of the same launch (reduce_fold_kernel): read it through L2
+  const double *gl = f.gamma + (size_t)e.lower * f.K, *gu = f.gamma + (size_t)e.upper * f.K;
+#pragma unroll
+  for (int k = 0; k < KC; ++k) {
+    double c = 0.0;
+    if (k < f.K) c = (e.lower == e.upper) ? __ldcg(gl + k) : __ldcg(gu + k) * e.upper_w + __ldcg(gl + k) * e.lower_w;
+    t->c[d][k] = c;
+  }
+}
+
+template <int KC>
+__global__ void fold_tables_kernel(FoldArgs f) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < f.G * 3) fold_item<KC>(f, i);
+}
+
+// The per-step reduction and the table fold in one launch: every CTA reduces one next-grid point; the CTA that finishes
+// last (device-wide counter) has all of gamma in front of it and folds the point tables of the step.  Saves a dependent
+// launch that would otherwise queue behind the basis kernel of the second stream.
+template <int KC>
+__global__ void __launch_bounds__(kReduceThreads) reduce_fold_kernel(ReduceArgs r, FoldArgs f, unsigned int *counter) {
+  reduce_partials_body(r);
+  __shared__ bool s_last;
+  __threadfence();  // this CTA's gamma row is visible device-wide before it is counted
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int i = threadIdx.x; i < f.G * 3; i += blockDim.x) fold_item<KC>(f, i);
+  if (threadIdx.x == 0) *counter = 0u;  // ready for the next launch
 }
 
 // base + row * pitch_bytes as one IMAD.WIDE (the compiler otherwise widens the 32-bit pitch and adds a zero high word)
@@ -698,6 +727,22 @@ size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta) 
   const int ACC = KP <= 8 ? 8 : 16;
   return point_table_bytes(K) * kRingTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kRingWarps * kBlockG * ACC) +
          (size_t)ring_rows * kRowBytes;
+}
+
+template <int KC>
+void launch_reduce_fold_for_kc(const ReduceArgs &r, const FoldArgs &f, unsigned int *counter, cudaStream_t stream) {
+  reduce_fold_kernel<KC><<<r.G, kReduceThreads, 0, stream>>>(r, f, counter);
+}
+
+void launch_reduce_fold(const ReduceArgs &r, const FoldArgs &f, unsigned int *counter, cudaStream_t stream) {
+  switch (coef_width(padded_basis(f.K))) {
+    case 2: launch_reduce_fold_for_kc<2>(r, f, counter, stream); break;
+    case 4: launch_reduce_fold_for_kc<4>(r, f, counter, stream); break;
+    case 6: launch_reduce_fold_for_kc<6>(r, f, counter, stream); break;
+    case 8: launch_reduce_fold_for_kc<8>(r, f, counter, stream); break;
+    case 12: launch_reduce_fold_for_kc<12>(r, f, counter, stream); break;
+    default: launch_reduce_fold_for_kc<16>(r, f, counter, stream); break;
+  }
 }
 
 void launch_fold_tables(const FoldArgs &f, cudaStream_t stream) {

@@ -23,6 +23,7 @@
 #include "dd.cuh"
 #include "device_types.hpp"
 #include "kernels.hpp"
+#include "reduce_partials.cuh"
 
 namespace lsmc {
 
@@ -542,62 +543,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_BACKWARD_MIN_CTAS) backward_ste
 
 // gamma[g][k] = sum over chunks of partials[g][chunk][k], in a fixed order; one CTA per grid point.
 // mean_mode: gamma[g][0] = sum / total_paths (the sample mean of LSV.cs:181), the other components are zero.
-constexpr int kReduceThreads = 1024;  // stride = 1024 / (acc_k / 2) residue classes: a multiple of 16 for acc_k = 8 and 16
-__global__ void __launch_bounds__(kReduceThreads) reduce_partials_kernel(ReduceArgs a) {
-  const int g = blockIdx.x;
-  // This grid point's partial sums are one contiguous run [num_chunks][acc_k].  A thread owns one pair of components
-  // (one 16-byte load) of every `stride`-th chunk and keeps eight loads in flight; everything is combined in a fixed order.
-  const int pairs = a.acc_k / 2;
-  const int kp = threadIdx.x % pairs;
-  const int lane_c = threadIdx.x / pairs;  // residue class of chunks
-  const int stride = blockDim.x / pairs;
-  const double2 *src = reinterpret_cast<const double2 *>(a.partials + (size_t)g * a.num_chunks * a.acc_k) + kp;
-  double2 s[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) s[i] = make_double2(0.0, 0.0);
-  int c = lane_c;
-  for (; c + 7 * stride < a.num_chunks; c += 8 * stride) {
-    double2 v[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = src[(size_t)(c + i * stride) * pairs];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      s[i].x += v[i].x;
-      s[i].y += v[i].y;
-    }
-  }
-  for (int i = 0; c < a.num_chunks; c += stride, ++i) {
-    const double2 v = src[(size_t)c * pairs];
-    s[i & 7].x += v.x;
-    s[i & 7].y += v.y;
-  }
-  double2 sum;
-  sum.x = ((s[0].x + s[1].x) + (s[2].x + s[3].x)) + ((s[4].x + s[5].x) + (s[6].x + s[7].x));
-  sum.y = ((s[0].y + s[1].y) + (s[2].y + s[3].y)) + ((s[4].y + s[5].y) + (s[6].y + s[7].y));
-  // combine the residue classes in a fixed order, in two levels: 16 runs of stride/16 classes, then the 16 run totals
-  __shared__ double2 s_all[kReduceThreads];
-  __shared__ double s_run[16][16];
-  s_all[threadIdx.x] = sum;
-  __syncthreads();
-  if (threadIdx.x < 16 * a.acc_k) {
-    const int k = threadIdx.x % a.acc_k, run = threadIdx.x / a.acc_k;
-    const int per_run = stride / 16;
-    double total = 0.0;
-    for (int cc = run * per_run; cc < (run + 1) * per_run; ++cc) {
-      const double2 v = s_all[cc * pairs + (k >> 1)];
-      total += (k & 1) ? v.y : v.x;
-    }
-    s_run[run][k] = total;
-  }
-  __syncthreads();
-  if (threadIdx.x < a.K) {
-    double total = 0.0;
-    for (int run = 0; run < 16; ++run) total += s_run[run][threadIdx.x];
-    double out = total;
-    if (a.mean_mode) out = (threadIdx.x == 0) ? total / (double)a.total_paths : 0.0;
-    a.out[(size_t)g * a.K + threadIdx.x] = out;
-  }
-}
+__global__ void __launch_bounds__(kReduceThreads) reduce_partials_kernel(ReduceArgs a) { reduce_partials_body(a); }
 
 // ------------------------------------------------------------------------------------------------------------------
 // Forward simulation

@@ -72,6 +72,8 @@ size_t point_table_bytes(int K);
 size_t backward_sweep_smem_bytes(int K);
 size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta);
 void launch_fold_tables(const FoldArgs &f, cudaStream_t stream);
+// reduce_partials + fold_tables in one launch (single GPU): the last CTA to finish folds; `counter` is a zeroed device word
+void launch_reduce_fold(const ReduceArgs &r, const FoldArgs &f, unsigned int *counter, cudaStream_t stream);
 void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream);

@@ -102,6 +102,7 @@ struct lsmc_handle {
   DeviceBuffer<DevDecision> decisions;
   DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
+  DeviceBuffer<unsigned int> fold_counter;  // device-wide arrival counter of reduce_fold_kernel (self-resetting)
   std::vector<size_t> window_offset;  // per period: first block in sweep_blocks
   std::vector<int> sweep_ring_rows;   // per period: ring size of the row-ring sweep kernel (0: direct-load sweep kernel)
   DeviceBuffer<SweepBlock> sweep_blocks;  // [window_offset[p] + block] row windows of the row-ring sweep kernel
@@ -538,7 +539,26 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   cudaStreamWaitEvent(h->aux_stream, h->ev_prepass, 0);
   if (has_basis(P - 1)) launch_basis_for(P - 1);
   if (has_basis(P - 2)) launch_basis_for(P - 2);
-  auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this) {
+  auto uses_sweep = [&](int p) { return D == 3 && use_sweep; };
+  // per-grid-point records of step p: payoffs, weights, row offsets and the folded regression coefficients (needs gamma[p])
+  auto fold_args_for = [&](int p) {
+    const PeriodTables &pt = h->tables.periods[p];
+    FoldArgs f{};
+    f.G = (int)pt.grid.size();
+    f.Gn = (int)h->tables.periods[p + 1].grid.size();
+    f.K = K;
+    f.pitch = h->pitch;
+    f.decisions = h->decisions.ptr + h->table_offset[p] * D;
+    f.num_decisions = h->num_decisions.ptr + h->table_offset[p];
+    f.inventory_cost = h->inv_cost.ptr + h->table_offset[p];
+    f.gamma = h->gamma.ptr + (size_t)p * Gmax * K;
+    f.settle_df = h->settle_df[p];
+    f.fused_payoff = (h->flags & LSMC_REFERENCE_OPERATION_ORDER) ? 0 : 1;
+    f.ring_rows = h->sweep_ring_rows[p];
+    f.out = h->point_tables.ptr;
+    return f;
+  };
+  auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this, bool fold_done) {
     const PeriodTables &pt = h->tables.periods[p];
     if (has_basis(p - 1)) cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0);
     BackwardStepArgs a{};
@@ -575,7 +595,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.q_prev = has_basis(p - 1) ? q_buffer(p - 1) : nullptr;
     a.partials = h->partials.ptr;
     // split the inventory grid over several CTAs only when there are too few path tiles to fill the GPU
-    const bool sweep = !terminal && D == 3 && use_sweep;
+    const bool sweep = !terminal && uses_sweep(p);
     const int sub_size = sweep ? 8 : kMaxGridTile;
     const int subtiles = (a.G + sub_size - 1) / sub_size;
     const int64_t tiles = sweep ? (N + kSweepTilePaths - 1) / kSweepTilePaths : num_tiles;
@@ -585,24 +605,13 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     a.subtiles_per_cta = (subtiles + gsplit - 1) / gsplit;
     gsplit = (subtiles + a.subtiles_per_cta - 1) / a.subtiles_per_cta;
     if (sweep) {
-      // per-grid-point records: payoffs, weights, row offsets and the folded regression coefficients (needs this step's gamma)
-      FoldArgs f{};
-      f.G = a.G;
-      f.Gn = a.Gn;
-      f.K = K;
-      f.pitch = h->pitch;
-      f.decisions = a.decisions;
-      f.num_decisions = a.num_decisions;
-      f.inventory_cost = a.inventory_cost;
-      f.gamma = a.gamma;
-      f.settle_df = a.settle_df;
-      f.fused_payoff = a.fused_payoff;
-      f.ring_rows = h->sweep_ring_rows[p];
-      f.out = h->point_tables.ptr;
-      mark(p, 1);
-      launch_fold_tables(f, st);
-      mark(p, 2);
-      launches++;
+      if (!fold_done) {
+        const FoldArgs f = fold_args_for(p);
+        mark(p, 1);
+        launch_fold_tables(f, st);
+        mark(p, 2);
+        launches++;
+      }
       a.point_tables = h->point_tables.ptr;
       a.ring_rows = h->sweep_ring_rows[p];
       a.sweep_blocks = h->sweep_blocks.ptr + h->window_offset[p];
@@ -625,7 +634,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     }
     return (int)tiles;
   };
-  auto reduce_gamma = [&](int p, int G_next, int num_chunks) {
+  auto reduce_gamma = [&](int p, int G_next, int num_chunks) -> bool {  // true: the point tables of step p were folded as well
     // regression coefficients of V_{p+1} on period p's basis (LSV.cs:199-212) from the partial sums the kernel that
     // produced V_{p+1} left behind
     const bool mean_mode = (p == 0 && h->current_active);
@@ -641,6 +650,11 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     const int world = h->comm.world();
     if (world == 1) {
       r.out = dst;
+      if (uses_sweep(p)) {  // reduction and table fold in one launch
+        launch_reduce_fold(r, fold_args_for(p), h->fold_counter.ptr, st);
+        launches++;
+        return true;
+      }
       launch_reduce_partials(r, st);
       launches++;
     } else {
@@ -654,18 +668,19 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       launch_combine_ranks(h->gather_buf.ptr, world, count, K, mean_mode ? 1 : 0, (double)r.total_paths, dst, st);
       launches += 2;
     }
+    return false;
   };
 
   double *v_next = h->v_a.ptr, *v_this = h->v_b.ptr;
   const auto enqueue0 = std::chrono::steady_clock::now();
-  int chunks = launch_step(P, true, nullptr, v_next);
+  int chunks = launch_step(P, true, nullptr, v_next, false);
   const double back_step = 0.66 / P;  // BackwardPcntTime (LSV.cs:48,164)
   double prog = 0.0;
   for (int p = P - 1; p >= 0; --p) {
     check_cancel();
     mark(p, 0);
-    reduce_gamma(p, (int)h->tables.periods[p + 1].grid.size(), chunks);
-    chunks = launch_step(p, false, v_next, v_this);
+    const bool folded = reduce_gamma(p, (int)h->tables.periods[p + 1].grid.size(), chunks);
+    chunks = launch_step(p, false, v_next, v_this, folded);
     std::swap(v_next, v_this);
     prog += back_step;
     if (progress) progress(prog, user);
@@ -898,6 +913,8 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     const int64_t num_tiles = (h->N + kSweepTilePaths - 1) / kSweepTilePaths;  // the finer of the two kernels' tilings
     h->partials.allocate((size_t)num_tiles * h->Gmax * h->acc_k);
     h->point_tables.allocate((size_t)h->Gmax * point_table_bytes(h->K) / sizeof(double));
+    h->fold_counter.allocate(1);
+    CUDA_OK(cudaMemset(h->fold_counter.ptr, 0, sizeof(unsigned int)));
     h->qbuf[0].allocate((size_t)h->K * h->pitch);
     h->qbuf[1].allocate((size_t)h->K * h->pitch);
     h->qbuf[2].allocate((size_t)h->K * h->pitch);
