@@ -510,7 +510,10 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   const Table *tab = reinterpret_cast<const Table *>(a.point_tables) + gbeg;
   const uint32_t pitch_bytes = (uint32_t)a.pitch * 8u;
   const char *tile_rows = reinterpret_cast<const char *>(a.v_next + tile * kSweepTilePaths);
-  const SweepBlock *blk = a.sweep_blocks + bbeg;
+  // this CTA's row windows, staged in shared memory: the thread that issues a generation must not wait on global loads while
+  // the other warps wait for it at the block barrier
+  SweepBlock *blk = reinterpret_cast<SweepBlock *>(s_rows + (size_t)R * kRowBytes);  // [nblocks]
+  for (int i = threadIdx.x; i < nblocks; i += kRingThreads) blk[i] = a.sweep_blocks[bbeg + i];
   __shared__ __align__(8) uint64_t s_mbar[2];
 
   // Generation j = everything block j needs that is not resident yet: the rows its window adds to the ring and, every other
@@ -726,7 +729,7 @@ size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta) 
   const int KP = padded_basis(K);
   const int ACC = KP <= 8 ? 8 : 16;
   return point_table_bytes(K) * kRingTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kRingWarps * kBlockG * ACC) +
-         (size_t)ring_rows * kRowBytes;
+         (size_t)ring_rows * kRowBytes + (size_t)blocks_per_cta * sizeof(SweepBlock);
 }
 
 template <int KC>
