@@ -375,6 +375,9 @@ constexpr int kPairGap = kSweepTilePaths / 2;          // ... this many columns 
 constexpr int kRowBytes = kSweepTilePaths * 8;
 constexpr int kRingTabSub = 16, kRingTabRing = 2 * kRingTabSub;
 static_assert(kRingWarps == kSlots && 32 * kLanePaths == kSweepTilePaths, "one 128-path group per CTA");
+#ifndef LSMC_RING_PF_AHEAD
+#define LSMC_RING_PF_AHEAD 0  // generations ahead whose rows are requested into L2 (measured: 0 is fastest, the bulk copies cover the latency)
+#endif
 #ifndef LSMC_RING_MIN_CTAS
 #define LSMC_RING_MIN_CTAS 3
 #endif
@@ -519,7 +522,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   // Generation j = everything block j needs that is not resident yet: the rows its window adds to the ring and, every other
   // block, the next sub-tile of point records.  One elected thread posts the byte count on mbarrier j & 1 and issues the bulk
   // copies; everybody waits on that barrier's phase (j >> 1) & 1 before starting block j.
-  auto issue_generation = [&](int j) {  // one thread only
+  auto issue_generation = [&](int j) {  // one whole warp: lane 0 posts the byte count, then every lane issues one row
     uint64_t *bar = &s_mbar[j & 1];
     int first_row, first_slot, count;
     if (j == 0) {
@@ -531,18 +534,21 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
     const int sub = j >> 1;  // records of sub-tile `sub` travel with its first block's generation, one block ahead of its use
     const int rec_first = sub * kRingTabSub;
     const int rec_count = (j & 1) == 0 ? max(0, min(kRingTabSub, glimit - rec_first)) : 0;
-    mbar_expect_tx(bar, (uint32_t)count * kRowBytes + (uint32_t)rec_count * (uint32_t)sizeof(Table));
-    if (rec_count > 0) bulk_load(s_tab + (sub & 1) * kRingTabSub, tab + rec_first, (uint32_t)rec_count * (uint32_t)sizeof(Table), bar);
+    if (lane == 0) {
+      mbar_expect_tx(bar, (uint32_t)count * kRowBytes + (uint32_t)rec_count * (uint32_t)sizeof(Table));
+      if (rec_count > 0) bulk_load(s_tab + (sub & 1) * kRingTabSub, tab + rec_first, (uint32_t)rec_count * (uint32_t)sizeof(Table), bar);
+    }
+    __syncwarp();
 #pragma unroll 1
-    for (int i = 0; i < count; ++i) {
+    for (int i = lane; i < count; i += 32) {
       int slot_i = first_slot + i;
       if (slot_i >= R) slot_i -= R;
       bulk_load(s_rows + (size_t)slot_i * kRowBytes, row_address(tile_rows, (uint32_t)(first_row + i), pitch_bytes), kRowBytes, bar);
     }
-    if (j + 2 < nblocks) {  // ask L2 for the rows two generations further on
-      const int pf_first = blk[j + 1].hi + 1, pf_count = blk[j + 2].hi - blk[j + 1].hi;
+    if (LSMC_RING_PF_AHEAD > 0 && j + LSMC_RING_PF_AHEAD < nblocks) {  // ask L2 for the rows a few generations further on
+      const int pf_first = blk[j + LSMC_RING_PF_AHEAD - 1].hi + 1, pf_count = blk[j + LSMC_RING_PF_AHEAD].hi - blk[j + LSMC_RING_PF_AHEAD - 1].hi;
 #pragma unroll 1
-      for (int i = 0; i < pf_count; ++i) bulk_prefetch_l2(row_address(tile_rows, (uint32_t)(pf_first + i), pitch_bytes), kRowBytes);
+      for (int i = lane; i < pf_count; i += 32) bulk_prefetch_l2(row_address(tile_rows, (uint32_t)(pf_first + i), pitch_bytes), kRowBytes);
     }
   };
   if (threadIdx.x == 0) {
@@ -551,7 +557,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (warp == 0) {
     issue_generation(0);
     if (nblocks > 1) issue_generation(1);  // its records are the second sub-tile only from block 2 on: (1 & 1) != 0, rows only
   }
@@ -604,12 +610,14 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   const double *my_b = s_v + (size_t)row * kVPitch + 4 * CH * warp + col;      // B fragments of this warp's slice
   double *my_c = s_acc + (size_t)warp * ACC * kBlockG + row * kBlockG + 2 * col;  // C fragment: [k][g], two adjacent g per lane
 
-  auto combine = [&](int b) {  // partial sums of block b: the warps' slices added in warp order
-    if (threadIdx.x < kBlockG * ACC) {
-      const int k = threadIdx.x / kBlockG, g8 = threadIdx.x - k * kBlockG;
+  auto combine = [&](int b) {  // partial sums of block b: the warps' slices added in warp order; every warp takes a quarter
+    constexpr int kPerWarp = kBlockG * ACC / kRingWarps;  // 16 (or 32) items per warp
+    if (lane < kPerWarp) {
+      const int item = warp * kPerWarp + lane;
+      const int k = item / kBlockG, g8 = item - k * kBlockG;
       const int g = b * kBlockG + g8;
       if (g < glimit) {
-        const double *src = s_acc + (size_t)(b & 1) * kRingWarps * ACC * kBlockG + threadIdx.x;
+        const double *src = s_acc + (size_t)(b & 1) * kRingWarps * ACC * kBlockG + item;
         double sum = src[0];
 #pragma unroll
         for (int w = 1; w < kRingWarps; ++w) sum += src[(size_t)w * ACC * kBlockG];
@@ -623,7 +631,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   for (int b = 0; b < nblocks; ++b) {
     // every warp has finished block b-1 (barrier at the end of the previous iteration): the record half and the ring slots
     // that generation b+1 overwrites are free.  Generation 1 was issued in the prologue.
-    if (b > 0 && b + 1 < nblocks && threadIdx.x == 32 * (b & 3)) issue_generation(b + 1);
+    if (b > 0 && b + 1 < nblocks && warp == (b & 3)) issue_generation(b + 1);
     const int gA = b * kBlockG + warp, gB = gA + kSlots;
     const Table *tA = s_tab + (min(gA, last) & (kRingTabRing - 1));
     const Table *tB = s_tab + (min(gB, last) & (kRingTabRing - 1));
