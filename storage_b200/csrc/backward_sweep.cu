@@ -359,13 +359,15 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
 // Row-ring variant.  The profile of the kernel above shows the L1/shared-memory data pipe as the limiter: every warp reads
 // each grid point's record with broadcast loads (8 useful bytes per wavefront) and its rows of v_next through the same
 // pipe.  This variant halves the record traffic per path and removes the global loads from the evaluating threads:
-//   * a CTA is ONE group of 128 paths x 4 grid slots (4 warps); every lane owns FOUR adjacent paths, so one set of record
-//     loads serves 128 paths;
+//   * a CTA is ONE group of 128 paths x 4 grid slots (4 warps); every lane owns FOUR paths (two adjacent pairs 64 columns
+//     apart, so every 16-byte access of a warp is one contiguous 512-byte run), and one set of record loads serves 128 paths;
 //   * the window of v_next rows that a block of 8 grid points reads ([lo, hi], SweepBlock) lives in a shared-memory ring of
-//     R rows x 128 paths; while block b is evaluated the CTA copies the rows block b+1 adds with cp.async (no registers
-//     held; completion rides on the one barrier per block that the regression GEMM needs anyway) and asks L2 for the rows
-//     of block b+3.  Every row comes from HBM/L2 once per CTA and is read back with conflict-free LDS.128 at offsets the
-//     fold kernel precomputed.
+//     R rows x 128 paths.  While block b is evaluated, one warp issues "generation" b+1: a bulk asynchronous copy (TMA 1-D,
+//     cp.async.bulk) per 1 KB row that block b+1 adds, plus, every other block, one bulk copy of the next 16 point records;
+//     they complete by byte count on one of two alternating mbarriers, which everybody waits on before the single
+//     __syncthreads per block that the regression GEMM needs anyway.  No thread holds registers for data in flight and the
+//     copies do not cross the LSU data pipe.  Every row comes from HBM/L2 once per CTA and is read back with conflict-free
+//     LDS.128 at offsets the fold kernel precomputed.  (An extra L2 look-ahead was measured and is slower: off.)
 // The host uses it when the windows slide upwards and fit (lsmc_api.cu), otherwise the direct-load kernel above.
 // ------------------------------------------------------------------------------------------------------------------
 constexpr int kRingThreads = 128;
