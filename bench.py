@@ -329,8 +329,8 @@ def run_gpu(args):
                         "frac": achieved / peak, "peak_source": peak_src,
                         # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch at a full-width step (1M paths, 200 grid
                         # points; profiles/r01_backward_sweep_ring.txt), scaled to this run's paths and mean grid width
-                        "traffic": 3.377e9 * (n / 1.0e6) * (16.0 * mean_grid + 64.0) / (16.0 * 200 + 64.0),
-                        "traffic_source": "ncu --set full, one launch, profiles/r01_backward_sweep_ring.txt (1.035 x algorithmic)",
+                        "traffic": 3.376e9 * (n / 1.0e6) * (16.0 * mean_grid + 64.0) / (16.0 * 200 + 64.0),
+                        "traffic_source": "ncu --set full, one launch, profiles/r01_backward_sweep_ring.txt (1.034 x algorithmic)",
                         "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_ms": 1000.0 * avg_kernel_s,
                         "kernel_share_of_step": (kernel_ms / 1000.0 / args.steps) / step_s},
            "e2e": {"value": evals_total / e2e_s, "unit": "path*step*inventory-point evals/s", "h2d_bytes_per_step": int(h2d),
