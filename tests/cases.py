@@ -113,7 +113,8 @@ def simple_one_factor(num_sims=2000, num_days=60, seed=11, val_offset=-5, invent
     val_date = start + val_offset
     storage = simple_storage(start, end, terminal=kw.pop("terminal", None), loss=kw.pop("loss", 0.0))
     model = MultiFactorParameters.For1Factor(12.5, 0.95)
-    return _finish(storage, val_date, inventory, model, ONE_FACTOR_BASIS, num_sims, seed, grid_points, **kw)
+    basis = kw.pop("basis", None) or ONE_FACTOR_BASIS
+    return _finish(storage, val_date, inventory, model, basis, num_sims, seed, grid_points, **kw)
 
 
 RATCHETS_A = [(0.0, (-702.7, 650.0)), (15_000.0, (-785.0, 552.5)), (30_000.0, (-790.6, 512.8)), (40_000.0, (-825.6, 498.6)),
@@ -168,7 +169,7 @@ def three_factor_ratchets(num_sims=2000, num_days=60, seed=11, val_offset=-1, in
     val_date = start + val_offset
     storage = ratchet_storage(start, end, outages=outages, kind=kind)
     model = three_factor_model(start, end)
-    basis = BasisFunctionsBuilder.Ones + Sim.X0 + Sim.X0.Pow(2) + Sim.X1 + Sim.X2 + Sim.X0 * Sim.X1 + Sim.S
+    basis = kw.pop("basis", None) or (BasisFunctionsBuilder.Ones + Sim.X0 + Sim.X0.Pow(2) + Sim.X1 + Sim.X2 + Sim.X0 * Sim.X1 + Sim.S)
     return _finish(storage, val_date, inventory, model, basis, num_sims, seed, grid_points, **kw)
 
 

@@ -134,6 +134,33 @@ def test_larger_path_count_config1():
     check_case(cases.three_factor_ratchets(num_sims=20_000, num_days=60, seed=21, outages=False))
 
 
+@pytest.mark.parametrize("num_basis", [1, 2, 3])
+def test_narrow_bases(num_basis):
+    """Bases of one to three monomials (the constant alone regresses on the sample mean of every period)."""
+    from storage_b200 import BasisFunctionsBuilder
+    basis = BasisFunctionsBuilder.Ones
+    for power in range(1, num_basis):
+        basis = basis + BasisFunctionsBuilder.SpotPricePower(power)
+    check_case(cases.simple_one_factor(num_sims=1500, num_days=25, seed=23, basis=basis))
+
+
+@pytest.mark.parametrize("variant", ["row_ring", "direct_sweep", "general"])
+@pytest.mark.parametrize("num_basis", [10, 13])
+def test_wide_bases(monkeypatch, variant, num_basis):
+    """Bases of 10 and 13 monomials: the kernels' 12- and 16-wide instantiations (two 8-row blocks of regression sums per grid
+    block, 16-wide partial-sum rows), in all three backward kernels."""
+    from storage_b200 import BasisFunctionsBuilder, Sim
+    if variant == "direct_sweep":
+        monkeypatch.setenv("LSMC_SWEEP_RING", "0")
+    elif variant == "general":
+        monkeypatch.setenv("LSMC_SWEEP", "0")
+    basis = (BasisFunctionsBuilder.Ones + Sim.X0 + Sim.X0.Pow(2) + Sim.X1 + Sim.X2 + Sim.X0 * Sim.X1 + Sim.S + Sim.S.Pow(2)
+             + Sim.X1.Pow(2) + Sim.X2.Pow(2))
+    if num_basis == 13:
+        basis = basis + Sim.X0 * Sim.X2 + Sim.X1 * Sim.X2 + Sim.S * Sim.X0
+    check_case(cases.three_factor_ratchets(num_sims=3000, num_days=30, seed=17, basis=basis))
+
+
 @pytest.mark.parametrize("gsplit", ["1", "3"])
 @pytest.mark.parametrize("variant", ["row_ring", "direct_sweep", "general"])
 def test_backward_kernel_variants(monkeypatch, variant, gsplit):
