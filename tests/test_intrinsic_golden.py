@@ -172,3 +172,61 @@ def test_very_low_vol_lsmc_deltas_equal_intrinsic_volume_profile():  # LsmcStora
     net_volume = -profile[:, 1] - profile[:, 2]
     for i, day in enumerate(periods):
         assert round(abs(lsmc.Deltas[day] - net_volume[i]), 5) == 0.0  # Assert.Equal(expected, actual, precision: 5)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The reference's closed-form intrinsic tests (tests/Cmdty.Storage.Test/IntrinsicStorageValuationTest.cs:37-183)
+# ---------------------------------------------------------------------------------------------------------------------
+def _intrinsic_fixture(starting_inventory, fwd, current):  # GenerateValuationResults, :37-76
+    storage = (CmdtyStorage.Builder.WithActiveTimePeriod(Day(2019, 9, 1), Day(2019, 9, 30))
+               .WithConstantInjectWithdrawRange(-45.5, 56.6)
+               .WithConstantMinInventory(0.0)
+               .WithConstantMaxInventory(1000.0)
+               .WithPerUnitInjectionCost(0.8, lambda d: d)
+               .WithNoCmdtyConsumedOnInject()
+               .WithPerUnitWithdrawalCost(1.2, lambda d: d)
+               .WithNoCmdtyConsumedOnWithdraw()
+               .WithNoCmdtyInventoryLoss()
+               .WithNoInventoryCost()
+               .MustBeEmptyAtEnd()
+               .Build())
+    b = LsmcValuationParameters.Builder()
+    b.CurrentPeriod = current
+    b.Inventory = starting_inventory
+    b.ForwardCurve = fwd
+    b.Storage = storage
+    b.SettleDateRule = lambda d: Day(2019, 10, 5)  # WithMonthlySettlement({2019-09: 2019-10-05})
+    b.DiscountFactors = lambda present, cash_flow: 1.0
+    b.GridCalc = FixedSpacingStateSpaceGridCalc(10.0)
+    b.NumericalTolerance = 1e-10
+    b.BasisFunctions = BasisFunctionsBuilder.Ones
+    b.SimulateWithMultiFactorModelAndMersenneTwister(MultiFactorParameters.For1Factor(1.0, 0.1), 16, 1)
+    return oracle.intrinsic_calculate(FlatProblem(b.Build(), 16, 1))
+
+
+def _spread_curve(spread):  # :148-171
+    fwd = {d: 56.6 for d in Day(2019, 9, 15).EnumerateTo(Day(2019, 9, 22))}
+    fwd.update({d: 56.6 + spread for d in Day(2019, 9, 23).EnumerateTo(Day(2019, 9, 30))})
+    return fwd
+
+
+def test_intrinsic_backwardated_curve_has_zero_value_and_no_flows():  # :102-128
+    price, fwd = 59.95, {}
+    for d in Day(2019, 9, 1).EnumerateTo(Day(2019, 9, 30)):
+        fwd[d] = price
+        price -= 0.58
+    npv, profile = _intrinsic_fixture(0.0, fwd, Day(2019, 9, 15))
+    assert npv == 0.0
+    assert profile.shape[0] == 16  # 2019-09-15 .. 2019-09-30
+    assert np.all(profile[:, 1] == 0.0)
+
+
+def test_intrinsic_spread_below_cycle_cost_has_zero_value_and_no_flows():  # :130-146
+    npv, profile = _intrinsic_fixture(0.0, _spread_curve(1.99), Day(2019, 9, 15))
+    assert npv == 0.0
+    assert np.all(profile[:, 1] == 0.0)
+
+
+def test_intrinsic_spread_above_cycle_cost_earns_spread_minus_cost_on_the_cyclable_volume():  # :173-183
+    npv, _ = _intrinsic_fixture(0.0, _spread_curve(2.01), Day(2019, 9, 15))
+    assert round(abs(npv - 7 * 45.5 * 0.01), 10) == 0.0  # Assert.Equal(expected, actual, precision: 10)
