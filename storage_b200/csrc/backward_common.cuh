@@ -11,12 +11,7 @@ namespace lsmc {
 struct __align__(16) DecisionA {  // one LDS.128 each
   double neg_volume, neg_consumed, cost_npv, lower_w;
 };
-struct __align__(16) DecisionB {
-  double upper_w;
-  long long lower_off, upper_off;  // row offsets into v_next, in doubles
-  double pad;
-};
-struct __align__(16) DecisionR {  // ring variant: byte offsets of the two rows inside the shared-memory ring
+struct __align__(16) DecisionR {  // upper weight and the offsets (in doubles) of the two rows of v_next
   double upper_w;
   uint32_t lower_off, upper_off;
 };

@@ -3,17 +3,21 @@
 //   gram_kernel / cholesky_kernel   regression pre-pass: double-double Gram matrix of the monomial design matrix of every
 //                                   period (LSV.cs:838-855 PopulateDesignMatrix), its Cholesky factor R and R^-1, i.e. the
 //                                   thin-QR of LSV.cs:193-196 formed without ever materialising Q.
-//   backward_step_kernel            one backward-induction step (LSV.cs:240-338) for a (path tile x inventory-grid tile):
-//                                   continuation value = q(path) . gamma(grid point), decision argmax, storage value;
-//                                   fused with the accumulation of q_prev^T V for the regression of the next backward
-//                                   step, so every storage value is written once and read once.
-//   reduce_partials_kernel          fixed-order reduction of the per-chunk regression partial sums -> gamma (LSV.cs:204).
-//   forward_kernel                  the whole forward simulation (LSV.cs:390-521) in one launch: a thread carries its path
-//                                   through all periods; per-period sums are reduced per CTA in a fixed order.
+//   basis_kernel                    orthonormal basis rows Q = X R^-1 of one period's regression simulations, materialised.
+//   backward_step_kernel            the GENERAL backward-induction step (LSV.cs:240-338): any decision-table width
+//                                   (ExtraDecisions > 0) and the terminal step.  The usual three-decision tables run on
+//                                   the sweep kernels of backward_sweep.cu.  Continuation value = q(path) . c(grid point,
+//                                   decision), decision argmax, storage value; fused with the accumulation of q_prev^T V
+//                                   for the regression of the next backward step, so every storage value is written once
+//                                   and read once.
+//   reduce_partials_kernel          fixed-order reduction of the per-tile regression partial sums -> gamma (LSV.cs:204).
+//   forward_kernel                  the whole forward simulation (LSV.cs:390-521) in one launch: periods outer, a CTA's path
+//                                   tiles inner, path state in shared memory; per-period sums reduced per CTA in a fixed order.
 //   sum kernels                     deterministic reductions for NPV / standard error / backward NPV.
 //
-// HBM-bound FP64 streaming work: no tensor cores.  Paths are the contiguous dimension of every buffer so
-// warps read and write whole 128-byte lines; the storage-value slabs use a 256-byte row pitch and are stored as double2.
+// HBM-bound FP64 streaming work; the only tensor-core use is the skinny FP64 GEMM of the regression sums
+// (mma.sync m8n8k4 f64).  Paths are the contiguous dimension of every buffer so warps read and write whole 128-byte lines;
+// the storage-value slabs use a row pitch that is a multiple of 256 paths and are accessed as double2.
 #include <cuda_runtime.h>
 
 #include <cstdint>
