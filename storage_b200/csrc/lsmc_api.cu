@@ -12,6 +12,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "comm.hpp"
@@ -63,6 +64,86 @@ struct DeviceBuffer {
   }
 };
 
+// Host <-> device movement of whole simulation / result panels (the caller-supplied-simulation overload at production size is
+// 58 GB per path set).  The caller's arrays are pageable, so they are staged through two pinned buffers: while
+// the DMA engine moves chunk i, a few host threads copy chunk i+1 between the caller's array and the other buffer.
+class PinnedStager {
+ public:
+  static constexpr size_t kChunkBytes = size_t(64) << 20;
+  ~PinnedStager() {
+    for (int i = 0; i < 2; ++i) {
+      if (buf_[i]) cudaFreeHost(buf_[i]);
+      if (ev_[i]) cudaEventDestroy(ev_[i]);
+    }
+  }
+  void to_device(void *dst, const void *src, size_t bytes, cudaStream_t st) {
+    ensure();
+    char *d = static_cast<char *>(dst);
+    const char *s = static_cast<const char *>(src);
+    int i = 0;
+    for (size_t off = 0; off < bytes; off += kChunkBytes, i ^= 1) {
+      const size_t len = std::min(kChunkBytes, bytes - off);
+      CUDA_OK(cudaEventSynchronize(ev_[i]));  // the copy that last used this buffer has left it
+      host_copy(buf_[i], s + off, len);
+      CUDA_OK(cudaMemcpyAsync(d + off, buf_[i], len, cudaMemcpyHostToDevice, st));
+      CUDA_OK(cudaEventRecord(ev_[i], st));
+    }
+    CUDA_OK(cudaStreamSynchronize(st));
+  }
+  void to_host(void *dst, const void *src, size_t bytes, cudaStream_t st) {
+    ensure();
+    char *d = static_cast<char *>(dst);
+    const char *s = static_cast<const char *>(src);
+    size_t pending_off = 0, pending_len = 0;
+    int i = 0, pending_buf = -1;
+    for (size_t off = 0; off < bytes; off += kChunkBytes, i ^= 1) {
+      const size_t len = std::min(kChunkBytes, bytes - off);
+      CUDA_OK(cudaMemcpyAsync(buf_[i], s + off, len, cudaMemcpyDeviceToHost, st));
+      CUDA_OK(cudaEventRecord(ev_[i], st));
+      if (pending_buf >= 0) {  // drain the previous chunk while this one is in flight
+        CUDA_OK(cudaEventSynchronize(ev_[pending_buf]));
+        host_copy(d + pending_off, buf_[pending_buf], pending_len);
+      }
+      pending_buf = i, pending_off = off, pending_len = len;
+    }
+    if (pending_buf >= 0) {
+      CUDA_OK(cudaEventSynchronize(ev_[pending_buf]));
+      host_copy(d + pending_off, buf_[pending_buf], pending_len);
+    }
+  }
+
+ private:
+  void ensure() {
+    for (int i = 0; i < 2; ++i) {
+      if (!buf_[i]) CUDA_OK(cudaHostAlloc(&buf_[i], kChunkBytes, cudaHostAllocDefault));
+      if (!ev_[i]) {
+        CUDA_OK(cudaEventCreateWithFlags(&ev_[i], cudaEventDisableTiming));
+      }
+    }
+  }
+  static void host_copy(void *dst, const void *src, size_t bytes) {
+    constexpr size_t kSlice = size_t(8) << 20;
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t parts = std::min<size_t>({(bytes + kSlice - 1) / kSlice, size_t(hw), size_t(8)});
+    if (parts <= 1) {
+      std::memcpy(dst, src, bytes);
+      return;
+    }
+    std::vector<std::thread> pool;
+    const size_t per = (bytes / parts + 63) & ~size_t(63);
+    for (size_t t = 1; t < parts; ++t) {
+      const size_t off = t * per;
+      if (off >= bytes) break;
+      const size_t len = std::min(per, bytes - off);
+      pool.emplace_back([=] { std::memcpy(static_cast<char *>(dst) + off, static_cast<const char *>(src) + off, len); });
+    }
+    std::memcpy(dst, src, std::min(per, bytes));
+    for (auto &t : pool) t.join();
+  }
+  void *buf_[2] = {nullptr, nullptr};
+  cudaEvent_t ev_[2] = {nullptr, nullptr};
+};
+
 struct SimSet {
   bool ready = false;
   const double *spot = nullptr;  // [rows][N] device
@@ -94,6 +175,7 @@ struct lsmc_handle {
   int Gmax = 0, D = 0, acc_k = 8;
 
   cudaStream_t stream = nullptr;
+  PinnedStager stager;                         // pinned double buffer for whole-panel host <-> device copies
   cudaStream_t aux_stream = nullptr;          // basis rows of period p-3 are materialised here while step p-1 runs
   cudaEvent_t ev_basis[3] = {}, ev_step[3] = {}, ev_prepass = nullptr;
   SimSet sims[2];
@@ -951,12 +1033,12 @@ static lsmc_status set_sims_impl(lsmc_handle *h, int which, const double *spot, 
       for (int i = 0; i < h->F; ++i) s.factors[i] = factors[i];
     } else {
       s.owned_spot.allocate(count);
-      CUDA_OK(cudaMemcpyAsync(s.owned_spot.ptr, spot, count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      h->stager.to_device(s.owned_spot.ptr, spot, count * sizeof(double), h->stream);
       s.spot = s.owned_spot.ptr;
       for (int i = 0; i < h->F; ++i) {
         if (!factors[i]) throw Error(LSMC_ERR_ARGUMENT, "a factor simulation panel is null");
         s.owned_factors[i].allocate(count);
-        CUDA_OK(cudaMemcpyAsync(s.owned_factors[i].ptr, factors[i], count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        h->stager.to_device(s.owned_factors[i].ptr, factors[i], count * sizeof(double), h->stream);
         s.factors[i] = s.owned_factors[i].ptr;
       }
       CUDA_OK(cudaStreamSynchronize(h->stream));
@@ -1079,7 +1161,7 @@ lsmc_status lsmc_copy_panel(lsmc_handle *h, lsmc_panel which, double *dst) {
     const size_t N = h->N;
     auto copy = [&](const double *src, size_t count) {
       if (!src) throw Error(LSMC_ERR_INVALID_OPERATION, "This panel was not requested in SimulationDataReturned.");
-      CUDA_OK(cudaMemcpy(dst, src, count * sizeof(double), cudaMemcpyDeviceToHost));
+      h->stager.to_host(dst, src, count * sizeof(double), h->stream);
     };
     switch (which) {
       case LSMC_PANEL_INVENTORY: copy(h->panels[0].ptr, (h->P + 1) * N); break;
@@ -1095,7 +1177,7 @@ lsmc_status lsmc_copy_panel(lsmc_handle *h, lsmc_panel which, double *dst) {
       case LSMC_PANEL_FACTORS_VALUATION: {
         const SimSet &s = h->sims[which == LSMC_PANEL_FACTORS_REGRESSION ? 0 : 1];
         for (int i = 0; i < h->F; ++i)
-          CUDA_OK(cudaMemcpy(dst + (size_t)i * h->sim_rows * N, s.factors[i], (size_t)h->sim_rows * N * sizeof(double), cudaMemcpyDeviceToHost));
+          h->stager.to_host(dst + (size_t)i * h->sim_rows * N, s.factors[i], (size_t)h->sim_rows * N * sizeof(double), h->stream);
         break;
       }
       default: throw Error(LSMC_ERR_ARGUMENT, "unknown panel");

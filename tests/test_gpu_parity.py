@@ -181,3 +181,20 @@ def test_grid_split_of_direct_kernel(monkeypatch):
     production path counts) instead of one sub-tile per CTA."""
     monkeypatch.setenv("LSMC_GSPLIT", "1")
     check_case(cases.three_factor_ratchets(num_sims=1500, num_days=40, seed=14))
+
+
+def test_caller_simulation_panels_larger_than_one_staging_chunk_round_trip():
+    """UseSpotSimResults at a size where every panel spans several 64 MB chunks of the pinned staging pipeline
+    (lsmc_set_sims in, lsmc_copy_panel out): what comes back is bit for bit what went in, and the valuation runs."""
+    import time
+    case = cases.simple_one_factor(num_sims=400_000, num_days=50, seed=3,
+                                   flags=SimulationDataReturned.AllSpotPrices | SimulationDataReturned.Inventory)
+    assert case.reg_spot.nbytes > 2 * (64 << 20)
+    t0 = time.perf_counter()
+    res = cases.run_gpu(case, keep_decisions=False)
+    dt = time.perf_counter() - t0
+    np.testing.assert_array_equal(res.RegressionSpotPriceSim, case.reg_spot)
+    np.testing.assert_array_equal(res.ValuationSpotPriceSim, case.val_spot)
+    assert res.InventoryBySim.shape == (case.flat.num_periods + 1, 400_000)
+    assert np.isfinite(res.Npv)
+    print(f"400k x 55 panels in and out, valuation included: {dt:.2f} s")
