@@ -376,6 +376,8 @@ constexpr int kLanePaths = 4;                          // paths per lane: two ad
 constexpr int kPairGap = kSweepTilePaths / 2;          // ... this many columns apart
 constexpr int kRowBytes = kSweepTilePaths * 8;
 constexpr int kRingTabSub = 16, kRingTabRing = 2 * kRingTabSub;
+constexpr int kVBufs = 4;    // regression value tiles in flight (the warps of a CTA may be a block apart, the GEMM runs a block behind)
+constexpr int kAccBufs = 3;  // regression-sum slice sets in flight
 static_assert(kRingWarps == kSlots && 32 * kLanePaths == kSweepTilePaths, "one 128-path group per CTA");
 #ifndef LSMC_RING_PF_AHEAD
 #define LSMC_RING_PF_AHEAD 0  // generations ahead whose rows are requested into L2 (measured: 0 is fastest, the bulk copies cover the latency)
@@ -453,6 +455,9 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
@@ -487,9 +492,9 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   using Table = PointTable<KC>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Table *s_tab = reinterpret_cast<Table *>(smem_raw);                        // [kRingTabRing]
-  double *s_v = reinterpret_cast<double *>(s_tab + kRingTabRing);            // [2][kBlockG][kVPitch]
-  double *s_acc = s_v + 2 * kBlockG * kVPitch;                               // [2][kRingWarps][ACC][kBlockG]
-  char *s_rows = reinterpret_cast<char *>(s_acc + 2 * kRingWarps * ACC * kBlockG);  // [R][kRowBytes]
+  double *s_v = reinterpret_cast<double *>(s_tab + kRingTabRing);            // [kVBufs][kBlockG][kVPitch]
+  double *s_acc = s_v + kVBufs * kBlockG * kVPitch;                          // [kAccBufs][kRingWarps][ACC][kBlockG]
+  char *s_rows = reinterpret_cast<char *>(s_acc + kAccBufs * kRingWarps * ACC * kBlockG);  // [R][kRowBytes]
   const int R = a.ring_rows;
 
   const int K = a.K;
@@ -519,7 +524,9 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   // the other warps wait for it at the block barrier
   SweepBlock *blk = reinterpret_cast<SweepBlock *>(s_rows + (size_t)R * kRowBytes);  // [nblocks]
   for (int i = threadIdx.x; i < nblocks; i += kRingThreads) blk[i] = a.sweep_blocks[bbeg + i];
-  __shared__ __align__(8) uint64_t s_mbar[2];
+  __shared__ __align__(8) uint64_t s_mbar[2];    // generation j landed (bulk copies, by byte count)
+  __shared__ __align__(8) uint64_t s_eval[2];    // every warp has evaluated block j (values published, ring rows released)
+  __shared__ __align__(8) uint64_t s_gemm[2];    // every warp has written its regression-sum slice of block j
 
   // Generation j = everything block j needs that is not resident yet: the rows its window adds to the ring and, every other
   // block, the next sub-tile of point records.  One elected thread posts the byte count on mbarrier j & 1 and issues the bulk
@@ -556,6 +563,10 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
   if (threadIdx.x == 0) {
     mbar_init(&s_mbar[0], 1);
     mbar_init(&s_mbar[1], 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_eval[i], kRingWarps);
+      mbar_init(&s_gemm[i], kRingWarps);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -619,7 +630,7 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
       const int k = item / kBlockG, g8 = item - k * kBlockG;
       const int g = b * kBlockG + g8;
       if (g < glimit) {
-        const double *src = s_acc + (size_t)(b & 1) * kRingWarps * ACC * kBlockG + item;
+        const double *src = s_acc + (size_t)(b % kAccBufs) * kRingWarps * ACC * kBlockG + item;
         double sum = src[0];
 #pragma unroll
         for (int w = 1; w < kRingWarps; ++w) sum += src[(size_t)w * ACC * kBlockG];
@@ -628,17 +639,39 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
     }
   };
 
-  mbar_wait(&s_mbar[0], 0);
+  // The four warps are NOT kept in lock step: instead of a block barrier each hand-off is an mbarrier that the producer
+  // warps arrive on (lane 0, after __syncwarp) and only the consumer of that hand-off waits on, so a warp may run up to a
+  // block ahead of the slowest one.  Buffer counts follow from that skew: a warp that has seen s_eval[j] complete knows every
+  // warp has finished iteration j-1 entirely.
+  //   s_eval[j]: block j evaluated by all  -> the GEMM of block j may read the tile; generation j+2 may overwrite the ring
+  //   s_gemm[j]: slices of block j written -> they may be combined
+  auto warp_arrive = [&](uint64_t *bar) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar);
+  };
+  auto gemm = [&](int bb) {  // C[k][g] = sum over the warp's 32 paths of q_prev[k][n] * V[g][n] for block bb
+    const double *vb = my_b + (bb % kVBufs) * (kBlockG * kVPitch);
+    double *dst = my_c + (bb % kAccBufs) * (kRingWarps * ACC * kBlockG);
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb) {
+      double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+      for (int j = 0; j < CH; ++j) dmma_m8n8k4(acc0, acc1, afrag[mb][j], vb[4 * j]);
+      *reinterpret_cast<double2 *>(dst + mb * 8 * kBlockG) = make_double2(acc0, acc1);
+    }
+  };
 
   for (int b = 0; b < nblocks; ++b) {
-    // every warp has finished block b-1 (barrier at the end of the previous iteration): the record half and the ring slots
-    // that generation b+1 overwrites are free.  Generation 1 was issued in the prologue.
-    if (b > 0 && b + 1 < nblocks && warp == (b & 3)) issue_generation(b + 1);
+    // generation b+1 overwrites ring slots and records that block b-1 was the last to read (generation 1: prologue)
+    if (b > 0 && b + 1 < nblocks && warp == (b & 3)) {
+      mbar_wait(&s_eval[(b - 1) & 1], ((b - 1) >> 1) & 1);
+      issue_generation(b + 1);
+    }
+    mbar_wait(&s_mbar[b & 1], (b >> 1) & 1);  // this block's rows and records have landed
     const int gA = b * kBlockG + warp, gB = gA + kSlots;
     const Table *tA = s_tab + (min(gA, last) & (kRingTabRing - 1));
     const Table *tB = s_tab + (min(gB, last) & (kRingTabRing - 1));
-    const int buf = b & 1;
-    double *vt = my_v + buf * (kBlockG * kVPitch);
+    double *vt = my_v + (b % kVBufs) * (kBlockG * kVPitch);
     {  // first point: evaluate, store, publish to the regression tile (its registers are free before the second point starts)
       double v[kLanePaths];
       evaluate4_ring<KP, KC, FUSED>(tA, my_rows, q, price, df, v);
@@ -665,25 +698,30 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
       }
     }
     vout += (uint64_t)kBlockG * pitch_bytes;
-    if (b + 1 < nblocks) mbar_wait(&s_mbar[(b + 1) & 1], ((b + 1) >> 1) & 1);  // rows and records of the next block have landed
-    __syncthreads();  // the regression tile is complete; nobody still reads what the next generation overwrites
+    warp_arrive(&s_eval[b & 1]);
     if (a.accumulate) {
-      // C[k][g] = sum over the warp's 32 paths of q_prev[k][n] * V[g][n]; C fragment: row -> k, columns 2 col + {0,1} -> g
-      const double *vb = my_b + buf * (kBlockG * kVPitch);
-      double *dst = my_c + buf * (kRingWarps * ACC * kBlockG);
-#pragma unroll
-      for (int mb = 0; mb < MB; ++mb) {
-        double acc0 = 0.0, acc1 = 0.0;
-#pragma unroll
-        for (int j = 0; j < CH; ++j) dmma_m8n8k4(acc0, acc1, afrag[mb][j], vb[4 * j]);
-        *reinterpret_cast<double2 *>(dst + mb * 8 * kBlockG) = make_double2(acc0, acc1);
+      if (b >= 1) {  // the regression sums run one block behind the evaluation
+        mbar_wait(&s_eval[(b - 1) & 1], ((b - 1) >> 1) & 1);
+        gemm(b - 1);
+        warp_arrive(&s_gemm[(b - 1) & 1]);
       }
-      if (b > 0) combine(b - 1);  // complete since the barrier above
+      if (b >= 2) {
+        mbar_wait(&s_gemm[(b - 2) & 1], ((b - 2) >> 1) & 1);
+        combine(b - 2);
+      }
     }
   }
-  if (a.accumulate) {
-    __syncthreads();
-    combine(nblocks - 1);
+  if (a.accumulate) {  // drain
+    const int bl = nblocks - 1;
+    mbar_wait(&s_eval[bl & 1], (bl >> 1) & 1);
+    gemm(bl);
+    warp_arrive(&s_gemm[bl & 1]);
+    if (bl >= 1) {
+      mbar_wait(&s_gemm[(bl - 1) & 1], ((bl - 1) >> 1) & 1);
+      combine(bl - 1);
+    }
+    mbar_wait(&s_gemm[bl & 1], (bl >> 1) & 1);
+    combine(bl);
   }
 }
 
@@ -738,7 +776,7 @@ size_t backward_sweep_smem_bytes(int K) {
 size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta) {
   const int KP = padded_basis(K);
   const int ACC = KP <= 8 ? 8 : 16;
-  return point_table_bytes(K) * kRingTabRing + sizeof(double) * (2 * kBlockG * kVPitch + 2 * kRingWarps * kBlockG * ACC) +
+  return point_table_bytes(K) * kRingTabRing + sizeof(double) * (kVBufs * kBlockG * kVPitch + kAccBufs * kRingWarps * kBlockG * ACC) +
          (size_t)ring_rows * kRowBytes + (size_t)blocks_per_cta * sizeof(SweepBlock);
 }
 
