@@ -364,9 +364,10 @@ __global__ void __launch_bounds__(kSweepThreads, LSMC_SWEEP_MIN_CTAS) backward_s
 //   * the window of v_next rows that a block of 8 grid points reads ([lo, hi], SweepBlock) lives in a shared-memory ring of
 //     R rows x 128 paths.  While block b is evaluated, one warp issues "generation" b+1: a bulk asynchronous copy (TMA 1-D,
 //     cp.async.bulk) per 1 KB row that block b+1 adds, plus, every other block, one bulk copy of the next 16 point records;
-//     they complete by byte count on one of two alternating mbarriers, which everybody waits on before the single
-//     __syncthreads per block that the regression GEMM needs anyway.  No thread holds registers for data in flight and the
-//     copies do not cross the LSU data pipe.  Every row comes from HBM/L2 once per CTA and is read back with conflict-free
+//     they complete by byte count on one of two alternating mbarriers, which everybody waits on before starting the block.
+//     There is no CTA barrier in the loop: the hand-offs between warps (block evaluated, GEMM slices written) are mbarriers
+//     that producers arrive on and only consumers wait on.  No thread holds registers for data in flight and the copies do
+//     not cross the LSU data pipe.  Every row comes from HBM/L2 once per CTA and is read back with conflict-free
 //     LDS.128 at offsets the fold kernel precomputed.  (An extra L2 look-ahead was measured and is slower: off.)
 // The host uses it when the windows slide upwards and fit (lsmc_api.cu), otherwise the direct-load kernel above.
 // ------------------------------------------------------------------------------------------------------------------
