@@ -194,6 +194,10 @@ typedef struct lsmc_results {
   double ms_backward_kernel;
   int64_t backward_kernel_launches;
   double ms_device;
+  /* Departure counter (DESIGN.md §2 "rounding at the inventory limits"): (path, period) pairs of the forward simulation whose
+     inventory had left [MinInventory, MaxInventory] by less than NumericalTolerance and was moved onto the limit, where the
+     reference throws (CmdtyStorage.cs:88-94).  0 means the run never relied on the departure. */
+  int64_t snapped_inventories;
 } lsmc_results;
 
 /* Per-sim panels selectable with SimulationDataReturned (LSV.cs:356-366,636-643). */

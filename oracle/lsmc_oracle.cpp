@@ -1118,6 +1118,7 @@ int oracle_lsmc_calculate(const lsmc_problem *pb, const double *reg_spot, const 
   }
 
   // ---------------------------------------------------------------------------- forward simulation (LSV.cs:356-612)
+  int64_t snapped_total = 0;  // (path, period) pairs moved onto an inventory limit (the documented departure below)
   std::vector<double> pv_by_sim(N, 0.0), deltas(P + 1, 0.0), profile((size_t)(P + 1) * 5, 0.0);
   std::vector<double> inv_this(N, pb->inventory), inv_next(N, 0.0);
   std::vector<lsmc_trigger_prices> trig(P);
@@ -1183,7 +1184,8 @@ int oracle_lsmc_calculate(const lsmc_problem *pb, const double *reg_spot, const 
 
     std::string loop_error;
     int loop_code = 0;
-#pragma omp parallel for schedule(static)
+    int64_t snapped_here = 0;
+#pragma omp parallel for schedule(static) reduction(+ : snapped_here)
     for (int64_t n = 0; n < N; n++) {  // LSV.cs:445-508
       try {
         double price = prices[n];
@@ -1194,8 +1196,8 @@ int oracle_lsmc_calculate(const lsmc_problem *pb, const double *reg_spot, const 
         // smaller than NumericalTolerance is snapped onto the limit instead (same rule in the CUDA forward kernel).
         {
           double lo = st.min_inventory(p), hi = st.max_inventory(p);
-          if (inventory < lo && lo - inventory <= tol) inventory = lo;
-          if (inventory > hi && inventory - hi <= tol) inventory = hi;
+          if (inventory < lo && lo - inventory <= tol) inventory = lo, snapped_here++;
+          if (inventory > hi && inventory - hi <= tol) inventory = hi, snapped_here++;
           inv_this[n] = inventory;
         }
         Range range = st.inject_withdraw_range(p, inventory);
@@ -1247,6 +1249,7 @@ int oracle_lsmc_calculate(const lsmc_problem *pb, const double *reg_spot, const 
       }
     }
     if (loop_code) throw OracleError(loop_code, loop_error);
+    snapped_total += snapped_here;
 
     // sequential accumulation in sim order, as the reference's single loop does (LSV.cs:490-507)
     double sum_spot_vol = 0.0, sum_vol = 0.0, sum_cons = 0.0, sum_loss = 0.0, sum_pv = 0.0;
@@ -1393,6 +1396,7 @@ int oracle_lsmc_calculate(const lsmc_problem *pb, const double *reg_spot, const 
     }
     variance /= (double)(N - 1);
   }
+  res->snapped_inventories = snapped_total;
   res->npv = forward_npv;
   res->std_error = std::sqrt(variance) / std::sqrt((double)N);
   res->backward_npv = mean_value(v_next[0].data(), N, 0);  // LSV.cs:623

@@ -158,6 +158,7 @@ def lsmc_calculate(flat, reg_spot, reg_factors, val_spot, val_factors, mode=1, t
     opt = oracle_options(mode, threads)
     _check(lib().oracle_lsmc_calculate(C.byref(pb), _dp(reg_spot), rp, _dp(val_spot), vp, C.byref(opt), C.byref(r), C.byref(pn)))
     out.npv, out.std_error, out.backward_npv = r.npv, r.std_error, r.backward_npv
+    out.snapped_inventories = int(r.snapped_inventories)  # forward-simulation inventories moved onto a limit (documented departure)
     return out
 
 

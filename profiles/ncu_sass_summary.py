@@ -8,6 +8,10 @@ rows = list(csv.reader(open(sys.argv[1])))
 hdr = rows[1]
 col = {h: i for i, h in enumerate(hdr)}
 data = rows[2:]
+for i, r in enumerate(data):  # ncu repeats the section once per view: keep the first
+    if r and r[0] == "Kernel Name":
+        data = data[:i]
+        break
 stall_cols = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
 tot = collections.Counter()
 ops = collections.Counter()

@@ -124,6 +124,7 @@ class lsmc_results(C.Structure):
         ("ms_backward_kernel", C.c_double),
         ("backward_kernel_launches", C.c_int64),
         ("ms_device", C.c_double),
+        ("snapped_inventories", C.c_int64),
     ]
 
 

@@ -106,6 +106,7 @@ struct ForwardArgs {
   // optional panels [P+1][N] (NULL = not requested)
   double *p_inventory, *p_volume, *p_consumed, *p_loss, *p_net_volume, *p_pv, *p_decision;
   int32_t *error_flag;             // set to an lsmc_status when a path leaves the feasible region
+  unsigned long long *snapped;     // count of (path, period) pairs whose inventory was moved onto a limit
 };
 
 }  // namespace lsmc

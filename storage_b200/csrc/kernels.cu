@@ -738,6 +738,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
     s_pv[t * kThreads + threadIdx.x] = 0.0;
   }
   int err = 0;
+  unsigned long long snapped = 0;  // inventories moved onto a limit (lsmc_results.snapped_inventories)
 
   for (int p = 0; p < a.P; ++p) {
     __syncthreads();  // previous period's shared tables are no longer in use
@@ -795,8 +796,8 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
 
       // LSV.cs:445-508 for this path.  A breach of the inventory limits smaller than NumericalTolerance (rounding of
       // inv + v - loss after a constrained decision) is snapped onto the limit; the reference would throw (CS.cs:88-94).
-      if (inventory < pp.min_inventory && pp.min_inventory - inventory <= a.tolerance) inventory = pp.min_inventory;
-      if (inventory > pp.max_inventory && inventory - pp.max_inventory <= a.tolerance) inventory = pp.max_inventory;
+      if (inventory < pp.min_inventory && pp.min_inventory - inventory <= a.tolerance) inventory = pp.min_inventory, snapped += valid;
+      if (inventory > pp.max_inventory && inventory - pp.max_inventory <= a.tolerance) inventory = pp.max_inventory, snapped += valid;
       DevRange range = storage_range_dev(a, pp, inventory, &err);
       const double loss = pp.loss * inventory;
       double decisions[LSMC_MAX_DECISIONS];
@@ -898,6 +899,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
     }
   }
   if (err) atomicExch(a.error_flag, err);
+  if (snapped) atomicAdd(a.snapped, snapped);  // integer sum: order-independent
 }
 
 // ------------------------------------------------------------------------------------------------------------------

@@ -507,8 +507,8 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   h->scalars.ms_valuation_sim = h->sims[1].ms_simulation;
   int64_t &launches = h->scalars.kernel_launches;
   auto wall0 = std::chrono::steady_clock::now();
-  int32_t zero = 0;
-  CUDA_OK(cudaMemcpyAsync(h->error_flag.ptr, &zero, sizeof(zero), cudaMemcpyHostToDevice, st));
+  // status block: [0] error flag (an lsmc_status), [2..3] 64-bit count of inventories moved onto a limit
+  CUDA_OK(cudaMemsetAsync(h->error_flag.ptr, 0, 4 * sizeof(int32_t), st));
   auto cancelled = [&] { return cancel && *cancel != 0; };
   auto check_cancel = [&] {
     if (cancelled()) {
@@ -829,6 +829,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.p_pv = h->panels[5].ptr;
   fa.p_decision = h->panels[6].ptr;
   fa.error_flag = h->error_flag.ptr;
+  fa.snapped = reinterpret_cast<unsigned long long *>(h->error_flag.ptr + 2);
   launch_forward(fa, fwd_ctas, st);
   launches++;
   dbg("forward_kernel", -1);
@@ -843,10 +844,13 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   CUDA_OK(cudaMemcpyAsync(h->h_gamma.data(), h->gamma.ptr, h->h_gamma.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
   h->h_rinv.resize((size_t)P * K * K * 2);
   CUDA_OK(cudaMemcpyAsync(h->h_rinv.data(), h->rinv.ptr, h->h_rinv.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
-  int32_t flag = 0;
-  CUDA_OK(cudaMemcpyAsync(&flag, h->error_flag.ptr, sizeof(flag), cudaMemcpyDeviceToHost, st));
+  int32_t status_block[4] = {0, 0, 0, 0};
+  CUDA_OK(cudaMemcpyAsync(status_block, h->error_flag.ptr, sizeof(status_block), cudaMemcpyDeviceToHost, st));
   CUDA_OK(cudaStreamSynchronize(st));
   CUDA_OK(cudaGetLastError());
+  const int32_t flag = status_block[0];
+  int64_t snapped = 0;
+  std::memcpy(&snapped, &status_block[2], sizeof(snapped));
   if (flag == LSMC_ERR_NUMERICAL)
     throw Error(LSMC_ERR_NUMERICAL, "Regression design matrix is rank deficient on the simulated paths (the reference's QR would return non-finite coefficients).");
   if (flag != 0)
@@ -914,6 +918,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   double final_inv_sum = device_sum(h, h->final_inv.ptr, N, 0.0, 1);
   h->comm.all_reduce_host(&final_inv_sum, 1, st);
 
+  h->scalars.snapped_inventories = snapped;
   h->scalars.npv = npv;
   h->scalars.std_error = std::sqrt(variance) / std::sqrt(total_n);
   h->scalars.backward_npv = back_sum / total_n;
@@ -1002,7 +1007,7 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     h->qbuf[2].allocate((size_t)h->K * h->pitch);
     h->pv.allocate(h->N);
     h->final_inv.allocate(h->N);
-    h->error_flag.allocate(1);
+    h->error_flag.allocate(4);
     h->block_sums.allocate(512);
     const uint32_t panel_flags[6] = {LSMC_RETURN_INVENTORY, LSMC_RETURN_INJECT_WITHDRAW_VOLUME, LSMC_RETURN_CMDTY_CONSUMED,
                                      LSMC_RETURN_INVENTORY_LOSS, LSMC_RETURN_NET_VOLUME, LSMC_RETURN_PV};

@@ -679,6 +679,7 @@ class LsmcStorageValuation:
         out.Timings["backward_kernel"] = r.ms_backward_kernel
         out.Timings["device"] = r.ms_device
         out.BackwardKernelLaunches = r.backward_kernel_launches
+        out.SnappedInventories = r.snapped_inventories
         flags = p.SimulationDataReturned
         S = SimulationDataReturned
         rows = len(flat.sim_periods)

@@ -4,9 +4,14 @@ fed through the caller-supplied-simulation overload (north star; SURVEY.md §8c 
 Tolerances (BASELINE.json north_star): NPV, deltas, profile within 1e-9 relative in FP64; argmax decisions identical.
 "Identical decisions" is checked on decision *volumes*: when the inventory-space bound makes two entries of a decision set
 coincide to ~1e-12 (e.g. max-rate withdrawal vs withdrawal constrained by the next step's maximum inventory) the index of
-the maximum is decided by the last ulp of the continuation value, so index flips between numerically identical decisions
-are reported but not counted as mismatches.
+the maximum is decided by the last ulp of the continuation value.  Every test therefore asserts: (1) wherever the argmax
+INDEX differs from the oracle's, the two decisions' volumes coincide to 1e-9 of the largest rate (the flip is a tie), and
+(2) no decision anywhere differs in volume by more than that.  The raw flip count of every case, against both oracle modes,
+is printed (`PARITY {...}` lines), appended to gpurun_out/parity_report.jsonl and recorded in BASELINE.md §4.
 """
+import json
+import os
+
 import numpy as np
 import pytest
 
@@ -17,35 +22,77 @@ from tests import cases
 pytestmark = pytest.mark.gpu
 
 REL = 1e-9
+VOLUME_TIE_REL = 1e-9  # two decisions are "the same volume" when they differ by less than this fraction of the largest rate
 
 
-def material_mismatches(gpu, ref):
+def decision_differences(gpu, ref):
+    """(raw index flips, largest |volume difference| at a flipped position, largest anywhere, positions whose volumes differ
+    by more than 1e-9 of the largest rate).  A raw flip is a different argmax INDEX at the same (period, path); it is a tie
+    when the two decisions' volumes coincide to rounding (see the module docstring)."""
     idx_diff = gpu.DecisionIndexBySim != ref.decision_index
-    vol_diff = np.abs(gpu.InjectWithdrawVolumeBySim[:-1] - ref.inject_withdraw_volume[:-1]) > 1e-6
-    return int(np.count_nonzero(idx_diff)), int(np.count_nonzero(vol_diff))
+    dvol = np.abs(gpu.InjectWithdrawVolumeBySim[:-1] - ref.inject_withdraw_volume[:-1])
+    scale = max(float(np.abs(ref.inject_withdraw_volume).max()), 1.0)
+    raw = int(np.count_nonzero(idx_diff))
+    at_flips = float(dvol[idx_diff].max()) if raw else 0.0
+    material = int(np.count_nonzero(dvol > VOLUME_TIE_REL * scale))
+    return raw, at_flips, float(dvol.max()), material, scale
 
 
-def check_case(case, rel=REL):
-    """Both arithmetic forms of the backward kernel (default fused payoff, and the reference's operation order) against the oracle."""
+_report_rows = []
+
+
+def report(case_name, case, against, form, raw, at_flips, anywhere, material, npv_rel, delta_rel, snapped):
+    """One line per (case, oracle mode, arithmetic form) on stdout (pytest -s / failure output) and in gpurun_out/."""
+    row = {"case": case_name, "paths": int(case.num_sims), "periods": int(case.flat.num_periods), "oracle": against, "kernel_form": form,
+           "decisions": int(case.num_sims) * int(case.flat.num_periods), "raw_index_flips": raw, "max_dvolume_at_flips": at_flips,
+           "max_dvolume": anywhere, "material_differences": material, "npv_rel": npv_rel, "delta_rel": delta_rel,
+           "inventories_snapped_onto_a_limit": snapped}
+    _report_rows.append(row)
+    print("PARITY " + json.dumps(row))
+    try:
+        out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+        os.makedirs(out_dir, exist_ok=True)
+        with open(os.path.join(out_dir, "parity_report.jsonl"), "a") as f:
+            f.write(json.dumps(row) + "\n")
+    except OSError:
+        pass
+
+
+def check_case(case, rel=REL, modes=("exact", "qr"), name=None):
+    """Both arithmetic forms of the backward kernel (default fused payoff, and the reference's operation order) against both
+    oracle modes: `exact` (the least-squares fit evaluated in double-double, rounded once) and `qr` (the reference's own
+    algorithm, thin QR -> R^-1 -> pinv in double, LSV.cs:193-206)."""
+    import inspect
+    name = name or inspect.stack()[1].function
     case.params.SimulationDataReturned = SimulationDataReturned.All
-    ref = oracle.lsmc_calculate(case.flat, case.reg_spot, case.reg_factors, case.val_spot, case.val_factors, mode=1)
+    refs = {m: oracle.lsmc_calculate(case.flat, case.reg_spot, case.reg_factors, case.val_spot, case.val_factors,
+                                     mode=1 if m == "exact" else 0) for m in modes}
     for reference_order in (False, True):
         gpu = cases.run_gpu(case, reference_operation_order=reference_order)
-        compare_with_oracle(case, gpu, ref, rel)
-    return gpu, ref
+        for m in modes:
+            compare_with_oracle(case, gpu, refs[m], rel, name=name, against=m, form="reference-order" if reference_order else "fused")
+    return gpu, refs[modes[0]]
 
 
-def compare_with_oracle(case, gpu, ref, rel):
-    raw, material = material_mismatches(gpu, ref)
-    assert material == 0, f"{material} material decision mismatches ({raw} raw index flips)"
+def compare_with_oracle(case, gpu, ref, rel, name="", against="exact", form="fused"):
+    raw, at_flips, anywhere, material, scale = decision_differences(gpu, ref)
+    periods = case.flat.periods
+    deltas = np.array([gpu.Deltas[p] for p in periods])
+    dscale = np.abs(ref.deltas).max() + 1e-300
+    report(name, case, against, form, raw, at_flips, anywhere, material, abs(gpu.Npv - ref.npv) / max(abs(ref.npv), 1e-300),
+           float(np.abs(deltas - ref.deltas).max() / dscale), int(gpu.SnappedInventories))
+    # the documented departure (inventory moved onto a limit where the reference throws) is taken equally often on both sides;
+    # a tie flip changes the inventory by rounding and with it, possibly, whether the next period needs the move
+    assert abs(gpu.SnappedInventories - ref.snapped_inventories) <= raw, (gpu.SnappedInventories, ref.snapped_inventories)
+    # argmax indices: every flip must be a tie (the two decisions inject/withdraw the same volume to rounding), and no
+    # position anywhere may differ in volume
+    assert at_flips <= VOLUME_TIE_REL * scale, f"{raw} index flips, one between volumes {at_flips:.3e} apart (not a tie)"
+    assert material == 0, f"{material} decisions differ in volume by more than {VOLUME_TIE_REL:g} of the rate ({raw} raw index flips)"
     assert gpu.Npv == pytest.approx(ref.npv, rel=rel)
     assert gpu.ValuationSimStandardError == pytest.approx(ref.std_error, rel=1e-8)
     assert gpu.BackwardNpv == pytest.approx(ref.backward_npv, rel=rel)
     P = case.flat.num_periods
-    periods = case.flat.periods
-    deltas = np.array([gpu.Deltas[p] for p in periods])
-    scale = np.abs(ref.deltas).max() + 1e-300
-    assert np.abs(deltas - ref.deltas).max() <= rel * scale
+    assert np.abs(deltas - ref.deltas).max() <= rel * dscale
     prof = np.array([[sp.Inventory, sp.InjectWithdrawVolume, sp.CmdtyConsumed, sp.InventoryLoss, sp.PeriodPv]
                      for sp in (gpu.ExpectedStorageProfile[p] for p in periods)])
     for col in range(5):
