@@ -25,6 +25,8 @@
 #include "device_types.hpp"
 #include "kernels.hpp"
 #include "reduce_partials.cuh"
+#include "mma_records.cuh"
+#include "sweep_common.cuh"
 
 #ifndef LSMC_SWEEP_PF
 #define LSMC_SWEEP_PF 8  // rows ahead of the window that are requested into L2
@@ -100,7 +102,11 @@ __device__ __forceinline__ void fold_item(const FoldArgs &f, int i) {  // i = 3 
 template <int KC>
 __global__ void fold_tables_kernel(FoldArgs f) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < f.G * 3) fold_item<KC>(f, i);
+  if (i >= fold_item_count(f)) return;
+  if (f.format == 1)
+    fold_item_mma(f, i);
+  else
+    fold_item<KC>(f, i);
 }
 
 // The per-step reduction and the table fold in one launch: every CTA reduces one next-grid point; the CTA that finishes
@@ -116,16 +122,16 @@ __global__ void __launch_bounds__(kReduceThreads) reduce_fold_kernel(ReduceArgs 
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  for (int i = threadIdx.x; i < f.G * 3; i += blockDim.x) fold_item<KC>(f, i);
+  const int items = fold_item_count(f);
+  for (int i = threadIdx.x; i < items; i += blockDim.x) {
+    if (f.format == 1)
+      fold_item_mma(f, i);
+    else
+      fold_item<KC>(f, i);
+  }
   if (threadIdx.x == 0) *counter = 0u;  // ready for the next launch
 }
 
-// base + row * pitch_bytes as one IMAD.WIDE (the compiler otherwise widens the 32-bit pitch and adds a zero high word)
-__device__ __forceinline__ const char *row_address(const char *base, uint32_t row, uint32_t pitch_bytes) {
-  const char *p;
-  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(p) : "r"(row), "r"(pitch_bytes), "l"(base));
-  return p;
-}
 // 16-byte load of this thread's two columns of row `row` (v_next is read-only for the whole launch)
 __device__ __forceinline__ double2 load_row(const char *base, uint32_t row, uint32_t pitch_bytes) {
   double2 v;
@@ -450,40 +456,6 @@ __device__ __forceinline__ void evaluate4_ring(const PointTable<KC> *__restrict_
   }
 }
 
-// Bulk asynchronous copies (the TMA engine's 1-D form) complete on an mbarrier by byte count: one instruction moves a whole
-// 1 KB row or a whole sub-tile of point records, no thread holds registers for it and nothing crosses the LSU data pipe.
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "DONE:\n\t"
-      "}" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void bulk_load(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
-               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void bulk_prefetch_l2(const void *src_gmem, uint32_t bytes) {
-  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
-}
-
 template <int KP, bool FUSED>
 __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_sweep_ring_kernel(BackwardStepArgs a) {
   constexpr int KC = (KP + 1) & ~1;
@@ -750,7 +722,7 @@ void launch_sweep_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaS
 
 template <int KC>
 void launch_fold_for_kc(const FoldArgs &f, cudaStream_t stream) {
-  fold_tables_kernel<KC><<<(f.G * 3 + 127) / 128, 128, 0, stream>>>(f);
+  fold_tables_kernel<KC><<<(fold_item_count(f) + 127) / 128, 128, 0, stream>>>(f);
 }
 
 int coef_width(int KP) { return (KP + 1) & ~1; }

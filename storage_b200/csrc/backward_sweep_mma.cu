@@ -1,0 +1,313 @@
+// backward_sweep_mma.cu — the backward-induction step (LSV.cs:240-338) for three-decision tables in the fused-payoff form,
+// with the payoff + regressed continuation value of every decision formed on the FP64 tensor path (mma.sync.m8n8k4.f64).
+//
+// Why.  The DFMA sweep kernel (backward_sweep.cu) is bound by instruction issue and by the FP64 pipe together: per 128
+// path x grid-point evaluations a warp issues ~340 instructions of which ~170 are FP64, and the FP64 pipe of B200 accepts one
+// warp-wide DFMA every ~2.2 cycles per scheduler (profiles/micro/fp64_pipes.cu).  DMMA runs on the same pipe at the same
+// FLOP rate (one m8n8k4 every 16 cycles per scheduler) but moves 256 FMAs per issued instruction instead of 32 and takes
+// its coefficient operand as a per-lane fragment instead of broadcast shared-memory loads.  The evaluation is therefore
+// re-cast as small GEMMs:
+//
+//   T_d[g][n] = offset_d(g) + sum_k c_d(g)[k] * qx[n][k]      d = 0,1,2     (8 grid points x 8 paths x K+1)
+//
+// where qx = (orthonormal basis row of the path, spot price of the path) and c_d(g) = (regression coefficients with the
+// next-grid interpolation folded in, (-v_d - consumed_d) * DF): T_d is the total the argmax is taken over (immediate cash
+// flow + regressed continuation value, LSV.cs:317-327).  The fragment layout puts grid point r = lane / 4 and the adjacent
+// paths 2c, 2c+1 (c = lane % 4) of an 8-path group in one lane, which is also what the rest of the step wants: the rows of
+// V_{p+1} are read as 16-byte pairs, V_p is stored as 16-byte pairs, and the values feed the regression GEMM of the next
+// backward step (Q_{p-1}^T V_p, also DMMA) straight from registers as its B fragments — no shared-memory exchange.
+//
+// Work layout.  A CTA owns 128 paths (4 warps x 32 paths = 4 groups of 8) and sweeps its range of the inventory grid upwards in
+// blocks of 8 grid points; every warp evaluates all 8 grid points of a block for its own paths.  The rows of V_{p+1} a block
+// reads live in a shared-memory ring filled by bulk asynchronous copies (TMA 1-D) kMmaLookAhead blocks ahead, together with
+// the block's record (mma_records.cuh); hand-offs are mbarriers, there is no CTA barrier in the loop.
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "backward_common.cuh"
+#include "device_types.hpp"
+#include "kernels.hpp"
+#include "mma_records.cuh"
+#include "sweep_common.cuh"
+
+#ifndef LSMC_MMA_MIN_CTAS
+#define LSMC_MMA_MIN_CTAS 3
+#endif
+
+namespace lsmc {
+
+namespace {
+
+constexpr int kMmaThreads = 128;
+constexpr int kMmaWarps = kMmaThreads / 32;
+constexpr int kMmaBlockG = 8;                     // grid points per block = m of the m8n8k4 tile
+constexpr int kMmaGroups = 4;                     // 8-path groups per warp
+constexpr int kMmaGens = kMmaLookAhead + 1;       // generations (rows + record of one block) in flight or in use
+constexpr int kMmaRowBytes = kSweepTilePaths * 8;
+static_assert(kMmaWarps * kMmaGroups * 8 == kSweepTilePaths, "4 warps x 4 groups x 8 paths = one 128-path tile");
+
+template <int KSTEPS, int MB>
+__global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep_mma_kernel(BackwardStepArgs a) {
+  using Rec = MmaBlockRecord<KSTEPS>;
+  constexpr int ACC = 8 * MB;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int R = a.ring_rows;
+  char *s_rows = reinterpret_cast<char *>(smem_raw);                                      // [R][kMmaRowPitchBytes]
+  Rec *s_rec = reinterpret_cast<Rec *>(s_rows + (size_t)R * kMmaRowPitchBytes);            // [kMmaGens]
+  double *s_acc = reinterpret_cast<double *>(s_rec + kMmaGens);                            // [2][kMmaWarps][ACC][8]
+  SweepBlock *blk = reinterpret_cast<SweepBlock *>(s_acc + 2 * kMmaWarps * ACC * kMmaBlockG);  // [nblocks]
+  __shared__ __align__(8) uint64_t s_mbar[kMmaGens];  // generation j landed (bulk copies, by byte count)
+  __shared__ __align__(8) uint64_t s_eval[kMmaGens];  // every warp has evaluated block j: its ring rows and record may be overwritten
+  __shared__ __align__(8) uint64_t s_gemm[2];         // every warp has written its regression-sum slice of block j
+
+  const int K = a.K;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int r = lane >> 2, c = lane & 3;
+  const int64_t tile = blockIdx.y;
+
+  const int total_blocks = (a.G + kMmaBlockG - 1) / kMmaBlockG;
+  const int bbeg = blockIdx.x * a.subtiles_per_cta;
+  const int nblocks = min(bbeg + a.subtiles_per_cta, total_blocks) - bbeg;
+  if (nblocks <= 0) return;
+  const int gbeg = bbeg * kMmaBlockG;
+  const int glimit = min(a.G, (bbeg + nblocks) * kMmaBlockG) - gbeg;  // grid points of this CTA, addressed 0..glimit-1 below
+
+  const Rec *recs = reinterpret_cast<const Rec *>(a.point_tables) + bbeg;
+  const uint32_t pitch_bytes = (uint32_t)a.pitch * 8u;
+  const char *tile_rows = reinterpret_cast<const char *>(a.v_next + tile * kSweepTilePaths);
+  for (int i = threadIdx.x; i < nblocks; i += kMmaThreads) blk[i] = a.sweep_blocks[bbeg + i];
+
+  // Generation j = what block j needs that is not resident yet: the rows its window adds to the ring and its record.
+  auto issue_generation = [&](int j) {  // one whole warp: lane 0 posts the byte count, then every lane issues one row
+    uint64_t *bar = &s_mbar[j % kMmaGens];
+    int first_row, first_slot, count;
+    if (j == 0) {
+      first_row = blk[0].lo, first_slot = blk[0].lo_slot, count = blk[0].hi - blk[0].lo + 1;
+    } else {
+      const SweepBlock cur = blk[j - 1], nxt = blk[j];
+      first_row = cur.hi + 1, first_slot = cur.hi_slot + 1, count = nxt.hi - cur.hi;
+    }
+    if (lane == 0) {
+      mbar_expect_tx(bar, (uint32_t)count * kMmaRowBytes + (uint32_t)sizeof(Rec));
+      bulk_load(s_rec + j % kMmaGens, recs + j, (uint32_t)sizeof(Rec), bar);
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int i = lane; i < count; i += 32) {
+      int slot_i = first_slot + i;
+      if (slot_i >= R) slot_i -= R;
+      bulk_load(s_rows + (size_t)slot_i * kMmaRowPitchBytes, row_address(tile_rows, (uint32_t)(first_row + i), pitch_bytes), kMmaRowBytes, bar);
+    }
+  };
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kMmaGens; ++i) {
+      mbar_init(&s_mbar[i], 1);
+      mbar_init(&s_eval[i], kMmaWarps);
+    }
+    mbar_init(&s_gemm[0], kMmaWarps);
+    mbar_init(&s_gemm[1], kMmaWarps);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 0)
+    for (int j = 0; j < min(kMmaGens, nblocks); ++j) issue_generation(j);
+
+  // ---- per-path operands, loaded once
+  // Columns in [N, pitch) are padding of the row buffers: zero in the basis rows and in the terminal values, hence finite in
+  // every row.  Lanes that own them compute on them like on any other column; a pair that straddles N is stored (and stays
+  // finite), a pair entirely beyond N is not.  Padding never reaches the regression sums: the q_prev fragments are zero there.
+  const int64_t warp_path0 = tile * kSweepTilePaths + 32 * warp;
+  // B fragments of qx = (basis row, spot price): lane (r, c) supplies coefficient 4 s + c of path 8 j + r of the warp
+  double qb[kMmaGroups][KSTEPS];
+#pragma unroll
+  for (int j = 0; j < kMmaGroups; ++j) {
+    const int64_t p = warp_path0 + 8 * j + r;
+#pragma unroll
+    for (int s = 0; s < KSTEPS; ++s) {
+      const int k = 4 * s + c;
+      double x = 0.0;
+      if (k < K)
+        x = a.q_this ? a.q_this[(size_t)k * a.pitch + p] : (k == 0 ? 1.0 : 0.0);  // mean mode: continuation value = gamma[g][0]
+      else if (k == K)
+        x = a.spot ? a.spot[min(p, a.N - 1)] : a.const_price;
+      qb[j][s] = x;
+    }
+  }
+  // the lane's own paths: 8 j + 2 c and + 1 of the warp
+  const int64_t own0 = warp_path0 + 2 * c;
+  double2 price[kMmaGroups];
+#pragma unroll
+  for (int j = 0; j < kMmaGroups; ++j) {
+    const int64_t p = own0 + 8 * j;
+    price[j] = a.spot ? make_double2(a.spot[min(p, a.N - 1)], a.spot[min(p + 1, a.N - 1)]) : make_double2(a.const_price, a.const_price);
+  }
+  // A fragments of the regression GEMM C[k][g] = sum_n q_prev[k][n] V[g][n]: lane (r, c) supplies basis function r (+ 8 mb) of
+  // path 2 c (.x) and 2 c + 1 (.y) of every group; the two halves are the two k4 chunks (even / odd paths) of the group
+  double2 qp[kMmaGroups][MB];
+#pragma unroll
+  for (int j = 0; j < kMmaGroups; ++j) {
+    const int64_t p = own0 + 8 * j;
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb) {
+      const int k = 8 * mb + r;
+      double2 x = make_double2(0.0, 0.0);
+      if (a.accumulate && k < K) {
+        if (a.q_prev)
+          x = *reinterpret_cast<const double2 *>(a.q_prev + (size_t)k * a.pitch + p);
+        else if (k == 0)
+          x = make_double2(1.0, 1.0);  // next regression is the sample mean: plain sum of V
+        if (p >= a.N) x.x = 0.0;
+        if (p + 1 >= a.N) x.y = 0.0;
+      }
+      qp[j][mb] = x;
+    }
+  }
+
+  const int last = glimit - 1;
+  const uint32_t own_col_bytes = (uint32_t)(32 * warp + 2 * c) * 8u;   // the lane's first pair inside a ring row
+  char *vout = reinterpret_cast<char *>(a.v_this + (size_t)(gbeg + r) * a.pitch + own0);
+  double *my_acc = s_acc + (size_t)warp * ACC * kMmaBlockG + r * kMmaBlockG + 2 * c;  // C fragment: [k][g], two adjacent g per lane
+
+  auto warp_arrive = [&](uint64_t *bar) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar);
+  };
+  auto combine = [&](int b) {  // partial sums of block b: the warps' slices added in warp order; every warp takes a quarter
+    constexpr int kPerWarp = kMmaBlockG * ACC / kMmaWarps;  // 16 (or 32) items per warp
+    if (lane < kPerWarp) {
+      const int item = warp * kPerWarp + lane;
+      const int k = item / kMmaBlockG, g8 = item - k * kMmaBlockG;
+      const int g = b * kMmaBlockG + g8;
+      if (g < glimit) {
+        const double *src = s_acc + (size_t)(b & 1) * kMmaWarps * ACC * kMmaBlockG + item;
+        double sum = src[0];
+#pragma unroll
+        for (int w = 1; w < kMmaWarps; ++w) sum += src[(size_t)w * ACC * kMmaBlockG];
+        a.partials[((size_t)(gbeg + g) * gridDim.y + tile) * ACC + k] = sum;
+      }
+    }
+  };
+
+  for (int b = 0; b < nblocks; ++b) {
+    // generation b + look-ahead overwrites ring slots and the record slot that block b - 1 was the last to read
+    if (b > 0 && b + kMmaLookAhead < nblocks && warp == (b & 3)) {
+      mbar_wait(&s_eval[(b - 1) % kMmaGens], ((b - 1) / kMmaGens) & 1);
+      issue_generation(b + kMmaLookAhead);
+    }
+    mbar_wait(&s_mbar[b % kMmaGens], (b / kMmaGens) & 1);  // this block's rows and record have landed
+    const Rec *rec = s_rec + b % kMmaGens;
+    MmaScalars sc[3];
+    uint2 rw[3];
+    double af[3][KSTEPS];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      sc[d] = rec->s[d][r];
+      rw[d] = rec->rows[d][r];
+#pragma unroll
+      for (int s = 0; s < KSTEPS; ++s) af[d][s] = rec->a[d][s][lane];
+    }
+    const bool store_g = b * kMmaBlockG + r <= last;
+    double2 racc[MB];
+#pragma unroll
+    for (int mb = 0; mb < MB; ++mb) racc[mb] = make_double2(0.0, 0.0);
+    const char *my_rows = s_rows + own_col_bytes;
+#pragma unroll
+    for (int j = 0; j < kMmaGroups; ++j) {
+      // totals the argmax is taken over, for grid point r and the paths 8 j + 2 c, + 1 (LSV.cs:317-327)
+      double t[3][2];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        t[d][0] = t[d][1] = sc[d].offset;
+#pragma unroll
+        for (int s = 0; s < KSTEPS; ++s) dmma_m8n8k4(t[d][0], t[d][1], af[d][s], qb[j][s]);
+      }
+      // value carried for a decision: immediate cash flow + realised continuation value (LSV.cs:296-302, 330-335), the weighted
+      // average of the two rows of V_{p+1}; an exact grid hit has lower == upper and weights (1, 0): the row itself
+      double2 w[3];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        const double2 lo = *reinterpret_cast<const double2 *>(my_rows + rw[d].x + j * 64);
+        const double2 up = *reinterpret_cast<const double2 *>(my_rows + rw[d].y + j * 64);
+        w[d].x = __fma_rn(price[j].x, sc[d].price_coef, __fma_rn(up.x, sc[d].upper_w, __fma_rn(lo.x, sc[d].lower_w, sc[d].offset)));
+        w[d].y = __fma_rn(price[j].y, sc[d].price_coef, __fma_rn(up.y, sc[d].upper_w, __fma_rn(lo.y, sc[d].lower_w, sc[d].offset)));
+      }
+      double2 v = w[0];
+      double best0 = t[0][0], best1 = t[0][1];
+#pragma unroll
+      for (int d = 1; d < 3; ++d) {  // first maximum wins (SH.cs:206-221)
+        if (t[d][0] > best0) {
+          best0 = t[d][0];
+          v.x = w[d].x;
+        }
+        if (t[d][1] > best1) {
+          best1 = t[d][1];
+          v.y = w[d].y;
+        }
+      }
+      if (store_g && own0 + 8 * j < a.N) *reinterpret_cast<double2 *>(vout + j * 64) = v;
+      if (a.accumulate) {
+#pragma unroll
+        for (int mb = 0; mb < MB; ++mb) {
+          dmma_m8n8k4(racc[mb].x, racc[mb].y, qp[j][mb].x, v.x);
+          dmma_m8n8k4(racc[mb].x, racc[mb].y, qp[j][mb].y, v.y);
+        }
+      }
+    }
+    vout += (uint64_t)kMmaBlockG * pitch_bytes;
+    warp_arrive(&s_eval[b % kMmaGens]);
+    if (a.accumulate) {
+      if (b >= 1) {  // slices of block b - 1 are complete once every warp has arrived; then its buffer is free for block b + 1
+        mbar_wait(&s_gemm[(b - 1) & 1], ((b - 1) >> 1) & 1);
+        combine(b - 1);
+      }
+      double *dst = my_acc + (size_t)(b & 1) * kMmaWarps * ACC * kMmaBlockG;
+#pragma unroll
+      for (int mb = 0; mb < MB; ++mb) *reinterpret_cast<double2 *>(dst + mb * 8 * kMmaBlockG) = racc[mb];
+      warp_arrive(&s_gemm[b & 1]);
+    }
+  }
+  if (a.accumulate) {
+    const int bl = nblocks - 1;
+    mbar_wait(&s_gemm[bl & 1], (bl >> 1) & 1);
+    combine(bl);
+  }
+}
+
+template <int KSTEPS, int MB>
+void launch_mma(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
+  cudaFuncSetAttribute(backward_sweep_mma_kernel<KSTEPS, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  backward_sweep_mma_kernel<KSTEPS, MB><<<grid, kMmaThreads, smem, stream>>>(a);
+}
+
+}  // namespace
+
+size_t mma_block_record_bytes(int K) { return mma_record_bytes(mma_ksteps(K)); }
+
+size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta) {
+  const int acc = K <= 8 ? 8 : 16;
+  return (size_t)ring_rows * kMmaRowPitchBytes + kMmaGens * mma_block_record_bytes(K) + sizeof(double) * 2 * kMmaWarps * acc * kMmaBlockG +
+         (size_t)blocks_per_cta * sizeof(SweepBlock);
+}
+
+void launch_backward_sweep_mma(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream) {
+  const dim3 grid(gsplit, (unsigned)num_tiles);
+  const size_t smem = backward_sweep_mma_smem_bytes(a.K, a.ring_rows, a.subtiles_per_cta);
+  const int ks = mma_ksteps(a.K);
+  const bool wide = a.K > 8;
+  static_assert(sizeof(MmaBlockRecord<2>) == 3 * 2 * 32 * 8 + 3 * 8 * 32 + 3 * 8 * 8, "record layout is what mma_record_bytes() says");
+  switch (ks) {
+    case 1: launch_mma<1, 1>(a, grid, smem, stream); break;
+    case 2: launch_mma<2, 1>(a, grid, smem, stream); break;
+    case 3:
+      if (wide)
+        launch_mma<3, 2>(a, grid, smem, stream);
+      else
+        launch_mma<3, 1>(a, grid, smem, stream);
+      break;
+    case 4: launch_mma<4, 2>(a, grid, smem, stream); break;
+    default: launch_mma<5, 2>(a, grid, smem, stream); break;
+  }
+}
+
+}  // namespace lsmc

@@ -54,7 +54,10 @@ struct FoldArgs {
   double settle_df;
   int fused_payoff;
   int ring_rows;                 // > 0: row offsets are written as slots of a ring of this many rows (row-ring sweep kernel)
-  void *out;                     // [G] records of point_table_bytes(K) each
+  int format;                    // 0: one PointTable per grid point (backward_sweep.cu); 1: one MmaBlockRecord per block of 8 grid
+                                 //    points (backward_sweep_mma.cu, mma_records.cuh)
+  int row_pitch_bytes;           // format 1: distance between two rows of the shared-memory ring
+  void *out;                     // format 0: [G] records of point_table_bytes(K) each; format 1: [ceil(G/8)] block records
 };
 
 int padded_basis(int K);
@@ -75,6 +78,12 @@ void launch_fold_tables(const FoldArgs &f, cudaStream_t stream);
 // reduce_partials + fold_tables in one launch (single GPU): the last CTA to finish folds; `counter` is a zeroed device word
 void launch_reduce_fold(const ReduceArgs &r, const FoldArgs &f, unsigned int *counter, cudaStream_t stream);
 void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
+// FP64-mma sweep kernel (backward_sweep_mma.cu): fused-payoff form only; look-ahead of kMmaLookAhead blocks in the row ring
+constexpr int kMmaLookAhead = 2;         // generations of rows requested ahead of the block being evaluated
+constexpr int kMmaRowPitchBytes = kSweepTilePaths * 8 + 64;  // consecutive ring rows start in opposite halves of the 32 banks
+size_t mma_block_record_bytes(int K);
+size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta);
+void launch_backward_sweep_mma(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream);
 // out[i] = sum over ranks r of all[r][i] (rank order); mean_mode: component 0 of every K-vector divided by total_paths, rest 0

@@ -164,6 +164,7 @@ struct lsmc_handle {
   bool current_active = false, discount_deltas = false, compat_terminal = true;
   uint32_t flags = 0;
   bool want_decisions = true;
+  bool use_mma = false;  // three-decision tables in the fused-payoff form run on the FP64-mma sweep kernel
   double inventory = 0, tolerance = 1e-10, grid_spacing = 0;
   int extra = 0;
   std::vector<double> forward_price, settle_df;
@@ -401,11 +402,12 @@ void build_device_tables(lsmc_handle *h) {
           lo[g / kGroup] = std::min(lo[g / kGroup], e.lower);
           hi[g / kGroup] = std::max(hi[g / kGroup], e.upper);
         }
-      // Row-ring sweep kernel (backward_sweep.cu): while block j is evaluated the rows block j+1 adds are copied in, so
-      // the ring must hold [lo(j), hi(j+1)] with hi a running maximum; usable when lo never decreases and the ring fits
-      // beside the kernel's other shared-memory buffers with two CTAs per SM.
+      // Row-ring sweep kernels (backward_sweep.cu, backward_sweep_mma.cu): while block j is evaluated the rows the next
+      // `look_ahead` blocks add are copied in, so the ring must hold [lo(j), hi(j+look_ahead)] with hi a running maximum; usable
+      // when lo never decreases and the ring fits beside the kernel's other shared-memory buffers with two CTAs per SM.
       {
         constexpr int kMaxSweepRing = 64;
+        const int look_ahead = h->use_mma ? kMmaLookAhead : 1;  // blocks whose rows are requested ahead of the one being evaluated
         const char *env = std::getenv("LSMC_SWEEP_RING");  // test hook: 0 forces the direct-load sweep kernel
         bool sweep_ok = !(env && env[0] == '0');
         std::vector<int32_t> hic(hi);
@@ -413,7 +415,7 @@ void build_device_tables(lsmc_handle *h) {
         int sweep_need = 0;
         for (int j = 0; j < groups; ++j) {
           if (j + 1 < groups && lo[j + 1] < lo[j]) sweep_ok = false;
-          sweep_need = std::max(sweep_need, hic[std::min(j + 1, groups - 1)] - lo[j] + 1);
+          sweep_need = std::max(sweep_need, hic[std::min(j + look_ahead, groups - 1)] - lo[j] + 1);
         }
         if (sweep_need > kMaxSweepRing) sweep_ok = false;
         const int R = sweep_ok ? std::max(sweep_need, 2) : 0;
@@ -637,6 +639,8 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     f.settle_df = h->settle_df[p];
     f.fused_payoff = (h->flags & LSMC_REFERENCE_OPERATION_ORDER) ? 0 : 1;
     f.ring_rows = h->sweep_ring_rows[p];
+    f.format = (h->use_mma && f.ring_rows > 0) ? 1 : 0;
+    f.row_pitch_bytes = kMmaRowPitchBytes;
     f.out = h->point_tables.ptr;
     return f;
   };
@@ -700,7 +704,9 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     }
     mark(p, 3);
     if (!terminal && time_steps) cudaEventRecord(step_events[2 * p], st);
-    if (sweep) {
+    if (sweep && h->use_mma && a.ring_rows > 0) {
+      launch_backward_sweep_mma(a, gsplit, tiles, st);
+    } else if (sweep) {
       launch_backward_sweep(a, gsplit, tiles, st);
     } else {
       launch_backward_step(a, gsplit, num_tiles, st);
@@ -999,7 +1005,12 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     CUDA_OK(cudaMemset(h->rinv.ptr, 0, h->rinv.count * sizeof(double)));
     const int64_t num_tiles = (h->N + kSweepTilePaths - 1) / kSweepTilePaths;  // the finer of the two kernels' tilings
     h->partials.allocate((size_t)num_tiles * h->Gmax * h->acc_k);
-    h->point_tables.allocate((size_t)h->Gmax * point_table_bytes(h->K) / sizeof(double));
+    {  // test hook: LSMC_SWEEP_MMA=0 keeps the fused form on the DFMA row-ring kernel
+      const char *env = std::getenv("LSMC_SWEEP_MMA");
+      h->use_mma = h->D == 3 && !(h->flags & LSMC_REFERENCE_OPERATION_ORDER) && !(env && env[0] == '0');
+    }
+    h->point_tables.allocate(std::max((size_t)h->Gmax * point_table_bytes(h->K),
+                                      (size_t)((h->Gmax + 7) / 8) * mma_block_record_bytes(h->K)) / sizeof(double));
     h->fold_counter.allocate(1);
     CUDA_OK(cudaMemset(h->fold_counter.ptr, 0, sizeof(unsigned int)));
     h->qbuf[0].allocate((size_t)h->K * h->pitch);

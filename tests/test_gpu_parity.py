@@ -191,13 +191,15 @@ def test_narrow_bases(num_basis):
     check_case(cases.simple_one_factor(num_sims=1500, num_days=25, seed=23, basis=basis))
 
 
-@pytest.mark.parametrize("variant", ["row_ring", "direct_sweep", "general"])
+@pytest.mark.parametrize("variant", ["row_ring", "row_ring_dfma", "direct_sweep", "general"])
 @pytest.mark.parametrize("num_basis", [10, 13])
 def test_wide_bases(monkeypatch, variant, num_basis):
     """Bases of 10 and 13 monomials: the kernels' 12- and 16-wide instantiations (two 8-row blocks of regression sums per grid
     block, 16-wide partial-sum rows), in all three backward kernels."""
     from storage_b200 import BasisFunctionsBuilder, Sim
-    if variant == "direct_sweep":
+    if variant == "row_ring_dfma":
+        monkeypatch.setenv("LSMC_SWEEP_MMA", "0")
+    elif variant == "direct_sweep":
         monkeypatch.setenv("LSMC_SWEEP_RING", "0")
     elif variant == "general":
         monkeypatch.setenv("LSMC_SWEEP", "0")
@@ -209,12 +211,15 @@ def test_wide_bases(monkeypatch, variant, num_basis):
 
 
 @pytest.mark.parametrize("gsplit", ["1", "3"])
-@pytest.mark.parametrize("variant", ["row_ring", "direct_sweep", "general"])
+@pytest.mark.parametrize("variant", ["row_ring", "row_ring_dfma", "direct_sweep", "general"])
 def test_backward_kernel_variants(monkeypatch, variant, gsplit):
-    """The three backward kernels against the oracle: the row-ring sweep kernel (default for three-decision tables whose row
-    windows slide upwards), the direct-load sweep kernel it falls back to, and the general kernel (any table width); each
-    with one CTA sweeping the whole grid of its path tile and with the grid split over several CTAs."""
-    if variant == "direct_sweep":
+    """The backward kernels against the oracle: the row-ring sweep kernels (default for three-decision tables whose row windows
+    slide upwards: FP64-mma evaluation for the fused form, DFMA evaluation for the reference's operation order and, with
+    LSMC_SWEEP_MMA=0, for both), the direct-load sweep kernel they fall back to, and the general kernel (any table width);
+    each with one CTA sweeping the whole grid of its path tile and with the grid split over several CTAs."""
+    if variant == "row_ring_dfma":
+        monkeypatch.setenv("LSMC_SWEEP_MMA", "0")
+    elif variant == "direct_sweep":
         monkeypatch.setenv("LSMC_SWEEP_RING", "0")
     elif variant == "general":
         monkeypatch.setenv("LSMC_SWEEP", "0")
