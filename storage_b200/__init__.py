@@ -8,5 +8,5 @@ from .cmdty_storage import (CmdtyStorage, ConstantInjectWithdrawConstraint, Inje
                             PiecewiseLinearInjectWithdrawConstraint, PolynomialInjectWithdrawConstraint,
                             StepInjectWithdrawConstraint)
 from .lsmc import (BasisFunctionsBuilder, FixedSpacingStateSpaceGridCalc, FlatProblem, Handle,  # noqa: F401
-                   LsmcStorageValuation, LsmcStorageValuationResults, LsmcValuationParameters, MultiFactorParameters,
+                   LsmcStorageValuation, LsmcStorageValuationResults, LsmcValuationParameters, MultiFactorParameters, PathShard,
                    PowerMonomialBuilder, Sim, SimulationDataReturned, SpotSimResultsFromPanels, StorageHelper)

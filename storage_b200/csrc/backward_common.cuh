@@ -19,6 +19,13 @@ struct __align__(16) DecisionR {  // upper weight and the offsets (in doubles) o
 constexpr int kWarpPaths = 32 * kPathsPerThread;  // 64 paths per warp
 constexpr int kTilePitch = kWarpPaths + 4;        // row pitch of the warp-private tiles: conflict-free fragment loads
 
+// d = a * b + c with separate accumulator-in and -out registers: the first mma of a chain reads its start value (a table
+// constant held for the whole block) without a copy
+__device__ __forceinline__ void dmma_m8n8k4_to(double &d0, double &d1, double a, double b, double c0, double c1) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%4,%5};"
+               : "=d"(d0), "=d"(d1)
+               : "d"(a), "d"(b), "d"(c0), "d"(c1));
+}
 __device__ __forceinline__ void dmma_m8n8k4(double &c0, double &c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1)

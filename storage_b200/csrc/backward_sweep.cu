@@ -132,6 +132,89 @@ __global__ void __launch_bounds__(kReduceThreads) reduce_fold_kernel(ReduceArgs 
   if (threadIdx.x == 0) *counter = 0u;  // ready for the next launch
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Sharded runs: the per-step chain  reduce partials -> exchange between ranks -> sum in rank order -> fold tables  as ONE
+// launch.  Every CTA reduces one next-grid point and stores its K sums straight into every rank's inbox (peer memory over
+// NVLink; this rank's own inbox included).  The CTA that finishes last publishes this rank's arrival flag on every peer, waits
+// until every rank's flag has arrived here, adds the world x G' x K sums in rank order (bit-identical on every rank) into
+// gamma and folds the step's tables.  Only that one CTA ever waits, after this rank's own data and flags are out, so ranks
+// cannot dead-lock on one another; a peer that never arrives (it failed or was cancelled) is given up on after timeout_ns
+// and reported through the error flag instead of hanging the GPU.
+// ------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <int KC>
+__global__ void __launch_bounds__(kReduceThreads) exchange_fold_kernel(ReduceArgs r, FoldArgs f, XchgArgs x, unsigned int *counter) {
+  const int count = r.G * r.K;
+  const size_t data_off = xchg_data_offset(x.world);
+  const size_t slot = ((size_t)(x.seq & 1) * x.world + x.rank) * x.capacity;  // this rank's slot in every inbox
+  __shared__ double s_sums[LSMC_MAX_BASIS];
+  {  // local sums of this CTA's grid point (mean mode is applied after the ranks are combined)
+    ReduceArgs local = r;
+    local.mean_mode = 0;
+    local.out = nullptr;
+    reduce_partials_body(local, s_sums);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < r.K * x.world; i += blockDim.x) {
+    const int peer = i / r.K, k = i - peer * r.K;
+    reinterpret_cast<double *>(x.peers[peer] + data_off)[slot + (size_t)blockIdx.x * r.K + k] = s_sums[k];
+  }
+  __shared__ bool s_last;
+  __threadfence_system();  // this CTA's sums are visible on every peer before it is counted
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence_system();
+  if (threadIdx.x < x.world)
+    st_release_sys(reinterpret_cast<unsigned long long *>(x.peers[threadIdx.x] + (size_t)x.rank * kXchgFlagStride), x.seq);
+  if (threadIdx.x < x.world) {
+    const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(x.peers[x.rank] + (size_t)threadIdx.x * kXchgFlagStride);
+    const unsigned long long t0 = global_timer_ns();
+    while (ld_acquire_sys(flag) < x.seq) {
+      if (*reinterpret_cast<volatile int32_t *>(x.error_flag) != 0) break;  // an earlier step already gave up: do not wait again
+      if (global_timer_ns() - t0 > x.timeout_ns) {
+        atomicCAS(x.error_flag, 0, (int)LSMC_ERR_CUDA);
+        break;
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+  __threadfence_system();
+  // gamma = sum over ranks, in rank order; the inbox was written by other GPUs: read it past L1
+  const double *inbox = reinterpret_cast<const double *>(x.peers[x.rank] + data_off) + (size_t)(x.seq & 1) * x.world * x.capacity;
+  for (int i = threadIdx.x; i < count; i += blockDim.x) {
+    double t = 0.0;
+    for (int s = 0; s < x.world; ++s) t += __ldcv(inbox + (size_t)s * x.capacity + i);
+    if (r.mean_mode) t = (i % r.K == 0) ? t / (double)r.total_paths : 0.0;
+    r.out[i] = t;
+  }
+  __threadfence();
+  __syncthreads();
+  const int items = f.G > 0 ? fold_item_count(f) : 0;
+  for (int i = threadIdx.x; i < items; i += blockDim.x) {
+    if (f.format == 1)
+      fold_item_mma(f, i);
+    else
+      fold_item<KC>(f, i);
+  }
+  if (threadIdx.x == 0) *counter = 0u;  // ready for the next launch
+}
+
 // 16-byte load of this thread's two columns of row `row` (v_next is read-only for the whole launch)
 __device__ __forceinline__ double2 load_row(const char *base, uint32_t row, uint32_t pitch_bytes) {
   double2 v;
@@ -766,6 +849,22 @@ void launch_reduce_fold(const ReduceArgs &r, const FoldArgs &f, unsigned int *co
     case 8: launch_reduce_fold_for_kc<8>(r, f, counter, stream); break;
     case 12: launch_reduce_fold_for_kc<12>(r, f, counter, stream); break;
     default: launch_reduce_fold_for_kc<16>(r, f, counter, stream); break;
+  }
+}
+
+template <int KC>
+void launch_exchange_fold_for_kc(const ReduceArgs &r, const FoldArgs &f, const XchgArgs &x, unsigned int *counter, cudaStream_t stream) {
+  exchange_fold_kernel<KC><<<r.G, kReduceThreads, 0, stream>>>(r, f, x, counter);
+}
+
+void launch_exchange_fold(const ReduceArgs &r, const FoldArgs &f, const XchgArgs &x, unsigned int *counter, cudaStream_t stream) {
+  switch (coef_width(padded_basis(r.K))) {
+    case 2: launch_exchange_fold_for_kc<2>(r, f, x, counter, stream); break;
+    case 4: launch_exchange_fold_for_kc<4>(r, f, x, counter, stream); break;
+    case 6: launch_exchange_fold_for_kc<6>(r, f, x, counter, stream); break;
+    case 8: launch_exchange_fold_for_kc<8>(r, f, x, counter, stream); break;
+    case 12: launch_exchange_fold_for_kc<12>(r, f, x, counter, stream); break;
+    default: launch_exchange_fold_for_kc<16>(r, f, x, counter, stream); break;
   }
 }
 

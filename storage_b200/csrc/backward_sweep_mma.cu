@@ -218,9 +218,9 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
       double t[3][2];
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
-        t[d][0] = t[d][1] = sc[d].offset;
+        dmma_m8n8k4_to(t[d][0], t[d][1], af[d][0], qb[j][0], sc[d].offset, sc[d].offset_again);
 #pragma unroll
-        for (int s = 0; s < KSTEPS; ++s) dmma_m8n8k4(t[d][0], t[d][1], af[d][s], qb[j][s]);
+        for (int s = 1; s < KSTEPS; ++s) dmma_m8n8k4(t[d][0], t[d][1], af[d][s], qb[j][s]);
       }
       // value carried for a decision: immediate cash flow + realised continuation value (LSV.cs:296-302, 330-335), the weighted
       // average of the two rows of V_{p+1}; an exact grid hit has lower == upper and weights (1, 0): the row itself
@@ -295,7 +295,7 @@ void launch_backward_sweep_mma(const BackwardStepArgs &a, int gsplit, int64_t nu
   const size_t smem = backward_sweep_mma_smem_bytes(a.K, a.ring_rows, a.subtiles_per_cta);
   const int ks = mma_ksteps(a.K);
   const bool wide = a.K > 8;
-  static_assert(sizeof(MmaBlockRecord<2>) == 3 * 2 * 32 * 8 + 3 * 8 * 32 + 3 * 8 * 8, "record layout is what mma_record_bytes() says");
+  static_assert(sizeof(MmaBlockRecord<2>) == 3 * 2 * 32 * 8 + 3 * 8 * sizeof(MmaScalars) + 3 * 8 * 8, "record layout is what mma_record_bytes() says");
   switch (ks) {
     case 1: launch_mma<1, 1>(a, grid, smem, stream); break;
     case 2: launch_mma<2, 1>(a, grid, smem, stream); break;

@@ -8,6 +8,9 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <vector>
+
+#include "kernels.hpp"
 
 namespace lsmc {
 
@@ -29,6 +32,15 @@ class Comm {
   void all_gather(const double *send, double *recv, size_t count, cudaStream_t stream);
   // sums n host doubles over ranks in rank order (no-op for a single rank); synchronises `stream`
   void all_reduce_host(double *values, size_t n, cudaStream_t stream);
+  // all[r][n] <- rank r's values[n] (host); synchronises `stream`
+  void all_gather_host(const double *values, size_t n, std::vector<double> &all, cudaStream_t stream);
+
+  // Peer-memory exchange of the per-step regression sums (kernels.hpp XchgArgs): every rank allocates one buffer, the
+  // ranks swap CUDA IPC handles through the communicator and map each other's buffers.  Returns false (and leaves the NCCL
+  // all-gather path in use) when the buffers cannot be mapped, e.g. ranks on different nodes or IPC disabled in the container.
+  bool setup_peer_exchange(size_t capacity_doubles, cudaStream_t stream);
+  bool peer_exchange_ready() const { return !peer_base_.empty(); }
+  XchgArgs next_exchange(int32_t *error_flag);  // arguments of the next exchange; every rank must call it equally often
 
  private:
   int world_ = 1, rank_ = 0;
@@ -37,6 +49,13 @@ class Comm {
   double *d_send_ = nullptr, *d_recv_ = nullptr;
   size_t staging_ = 0;
   void ensure_staging(size_t count);
+  // peer exchange
+  char *xchg_local_ = nullptr;
+  std::vector<char *> peer_base_;  // [world] mapped bases (own buffer at [rank])
+  char **d_peer_base_ = nullptr;
+  size_t xchg_capacity_ = 0;
+  unsigned long long xchg_seq_ = 0;
+  void release_peer_exchange();
 };
 
 }  // namespace lsmc

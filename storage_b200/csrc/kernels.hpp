@@ -60,6 +60,22 @@ struct FoldArgs {
   void *out;                     // format 0: [G] records of point_table_bytes(K) each; format 1: [ceil(G/8)] block records
 };
 
+// Peer-memory exchange of the per-step regression sums between the ranks of a sharded valuation (comm.cu PeerExchange).
+// Every rank owns one exchange buffer and maps every other rank's (CUDA IPC over NVLink):
+//   [world] arrival flags, 128 bytes apart: flags[s] = sequence number of the last exchange rank s has fully written here
+//   [2][world][capacity] doubles: inbox, one slot per (parity of the sequence number, source rank)
+struct XchgArgs {
+  char *const *peers;     // [world] base of every rank's exchange buffer as mapped here (own buffer at [rank])
+  int world, rank;
+  size_t capacity;        // doubles per inbox slot
+  unsigned long long seq; // this exchange's sequence number (same on every rank, increasing)
+  unsigned long long timeout_ns;  // give up waiting for a peer after this long (flags an error instead of hanging the GPU)
+  int32_t *error_flag;
+};
+constexpr size_t kXchgFlagStride = 128;
+__host__ __device__ inline size_t xchg_data_offset(int world) { return ((size_t)world * kXchgFlagStride + 255) / 256 * 256; }
+__host__ __device__ inline size_t xchg_buffer_bytes(int world, size_t capacity) { return xchg_data_offset(world) + 2 * (size_t)world * capacity * sizeof(double); }
+
 int padded_basis(int K);
 inline int acc_width(int K) { return padded_basis(K) <= 8 ? 8 : 16; }
 size_t backward_smem_bytes(int KP, int D);
@@ -77,9 +93,14 @@ size_t backward_sweep_ring_smem_bytes(int K, int ring_rows, int blocks_per_cta);
 void launch_fold_tables(const FoldArgs &f, cudaStream_t stream);
 // reduce_partials + fold_tables in one launch (single GPU): the last CTA to finish folds; `counter` is a zeroed device word
 void launch_reduce_fold(const ReduceArgs &r, const FoldArgs &f, unsigned int *counter, cudaStream_t stream);
+// sharded runs: reduce_partials + exchange with the other ranks over peer memory + rank-ordered sum + fold_tables in one launch
+void launch_exchange_fold(const ReduceArgs &r, const FoldArgs &f, const XchgArgs &x, unsigned int *counter, cudaStream_t stream);
 void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream);
 // FP64-mma sweep kernel (backward_sweep_mma.cu): fused-payoff form only; look-ahead of kMmaLookAhead blocks in the row ring
-constexpr int kMmaLookAhead = 2;         // generations of rows requested ahead of the block being evaluated
+#ifndef LSMC_MMA_LOOKAHEAD
+#define LSMC_MMA_LOOKAHEAD 2
+#endif
+constexpr int kMmaLookAhead = LSMC_MMA_LOOKAHEAD;  // generations of rows requested ahead of the block being evaluated
 constexpr int kMmaRowPitchBytes = kSweepTilePaths * 8 + 64;  // consecutive ring rows start in opposite halves of the 32 banks
 size_t mma_block_record_bytes(int K);
 size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta);

@@ -52,9 +52,10 @@ struct DeviceBuffer {
     ptr = nullptr;
     count = 0;
   }
-  void allocate(size_t n) {
-    release();
+  void allocate(size_t n) {  // contents are unspecified afterwards; an existing buffer of the right size is kept (handle re-use)
     if (n == 0) n = 1;
+    if (ptr && count == n) return;
+    release();
     CUDA_OK(cudaMalloc(&ptr, n * sizeof(T)));
     count = n;
   }
@@ -512,8 +513,10 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   // status block: [0] error flag (an lsmc_status), [2..3] 64-bit count of inventories moved onto a limit
   CUDA_OK(cudaMemsetAsync(h->error_flag.ptr, 0, 4 * sizeof(int32_t), st));
   auto cancelled = [&] { return cancel && *cancel != 0; };
+  // Sharded runs honour a cancellation after the device work, when the ranks exchange their status: a rank that stopped
+  // enqueueing on its own would leave the others waiting for it in the next per-step exchange.
   auto check_cancel = [&] {
-    if (cancelled()) {
+    if (cancelled() && h->comm.world() == 1) {
       cudaStreamSynchronize(st);
       cudaStreamSynchronize(h->aux_stream);
       throw Error(LSMC_ERR_CANCELLED, "The operation was canceled.");
@@ -745,6 +748,14 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       }
       launch_reduce_partials(r, st);
       launches++;
+    } else if (h->comm.peer_exchange_ready()) {
+      // local sums -> every rank's inbox over peer memory -> sum in rank order -> table fold, in one launch
+      r.out = dst;
+      FoldArgs f{};
+      if (uses_sweep(p)) f = fold_args_for(p);
+      launch_exchange_fold(r, f, h->comm.next_exchange(h->error_flag.ptr), h->fold_counter.ptr, st);
+      launches++;
+      return uses_sweep(p);
     } else {
       // local sums -> all-gather -> sum in rank order (identical on every rank)
       const int count = G_next * K;
@@ -854,9 +865,27 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   CUDA_OK(cudaMemcpyAsync(status_block, h->error_flag.ptr, sizeof(status_block), cudaMemcpyDeviceToHost, st));
   CUDA_OK(cudaStreamSynchronize(st));
   CUDA_OK(cudaGetLastError());
-  const int32_t flag = status_block[0];
+  int32_t flag = status_block[0];
   int64_t snapped = 0;
   std::memcpy(&snapped, &status_block[2], sizeof(snapped));
+  if (h->comm.world() > 1) {
+    // every rank must leave lsmc_run with the same status, or the ranks that carry on would wait for the one that threw in
+    // the next collective: exchange (status, snapped count, cancel seen) before acting on any of them
+    const double mine[3] = {(double)flag, (double)snapped, cancelled() ? 1.0 : 0.0};
+    std::vector<double> all;
+    h->comm.all_gather_host(mine, 3, all, st);
+    flag = 0;
+    snapped = 0;
+    bool any_cancel = false;
+    for (int r = 0; r < h->comm.world(); ++r) {
+      if (flag == 0) flag = (int32_t)all[3 * r];  // first failing rank, in rank order
+      snapped += (int64_t)all[3 * r + 1];
+      any_cancel = any_cancel || all[3 * r + 2] != 0.0;
+    }
+    if (any_cancel) throw Error(LSMC_ERR_CANCELLED, "The operation was canceled.");
+  }
+  if (flag == LSMC_ERR_CUDA)
+    throw Error(LSMC_ERR_CUDA, "A rank of the sharded valuation did not arrive at a per-step exchange within the time limit (it failed, was cancelled or is not running the same valuation).");
   if (flag == LSMC_ERR_NUMERICAL)
     throw Error(LSMC_ERR_NUMERICAL, "Regression design matrix is rank deficient on the simulated paths (the reference's QR would return non-finite coefficients).");
   if (flag != 0)
@@ -893,21 +922,33 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   h->pv_by_sim.clear();
   double npv, variance;
   if (need_pv_host) {
-    if (h->comm.world() > 1) throw Error(LSMC_ERR_UNSUPPORTED, "Terminal inventory value with sharded paths is not supported yet.");
     std::vector<double> pv(N), inv(N), s_end(N);
     CUDA_OK(cudaMemcpy(pv.data(), h->pv.ptr, N * sizeof(double), cudaMemcpyDeviceToHost));
     CUDA_OK(cudaMemcpy(inv.data(), h->final_inv.ptr, N * sizeof(double), cudaMemcpyDeviceToHost));
     CUDA_OK(cudaMemcpy(s_end.data(), h->sims[0].spot + (size_t)(P - h->first_sim) * N, N * sizeof(double), cudaMemcpyDeviceToHost));  // regression sims
     std::vector<double> last_row(h->panels[5].ptr ? N : 0);
-    double running = 0.0;
+    // Sharded: the reference's running sum runs over the paths in global order, so a rank starts from the total of
+    // the ranks before it (exclusive prefix of the per-rank totals, one scalar gathered per rank).
+    double local_total = 0.0;
     for (int64_t n = 0; n < N; ++n) {
-      const double t = h->model->terminal_npv(s_end[n], inv[n]);
+      s_end[n] = h->model->terminal_npv(s_end[n], inv[n]);  // terminal value of path n, in place
+      local_total += s_end[n];
+    }
+    std::vector<double> totals;
+    h->comm.all_gather_host(&local_total, 1, totals, st);
+    double running = 0.0, global_total = 0.0;
+    for (int r = 0; r < h->comm.world(); ++r) {
+      if (r < h->comm.rank()) running += totals[r];
+      global_total += totals[r];
+    }
+    for (int64_t n = 0; n < N; ++n) {
+      const double t = s_end[n];
       running += t;
       const double add = h->compat_terminal ? running : t;  // cumulative-sum quirk of LSV.cs:606-609
       pv[n] += add;
       if (!last_row.empty()) last_row[n] = add;
     }
-    end_period_pv = running / N;
+    end_period_pv = global_total / total_n;
     if (!last_row.empty()) CUDA_OK(cudaMemcpy(h->panels[5].ptr + (size_t)P * N, last_row.data(), N * sizeof(double), cudaMemcpyHostToDevice));
     CUDA_OK(cudaMemcpy(h->pv.ptr, pv.data(), N * sizeof(double), cudaMemcpyHostToDevice));
   }
@@ -1248,6 +1289,7 @@ lsmc_status lsmc_comm_init(lsmc_handle *h, const void *id, int rank, int world, 
   try {
     CUDA_OK(cudaSetDevice(h->device));
     h->comm.init(id, rank, world, total_sims);
+    h->comm.setup_peer_exchange((size_t)h->Gmax * h->K, h->stream);  // falls back to NCCL all-gathers when peers cannot be mapped
     return LSMC_OK;
   } catch (const std::exception &e) {
     return (lsmc_status)status_of(h, e);

@@ -21,7 +21,8 @@
 namespace lsmc {
 
 struct MmaScalars {
-  double offset, price_coef, lower_w, upper_w;
+  double offset, offset_again;  // twice: one 16-byte load fills the two-register start value of the mma accumulator pair
+  double price_coef, lower_w, upper_w, pad;
 };
 
 template <int KSTEPS>
@@ -47,7 +48,8 @@ __device__ __forceinline__ void fold_item_mma(const FoldArgs &f, int i) {
   const int nd = f.num_decisions[g];
   const DevDecision e = f.decisions[(size_t)g * 3 + (d < nd ? d : 0)];
   const double price_coef = (-e.volume - e.consumed) * f.settle_df;
-  *sc = MmaScalars{-(e.cost_npv + f.inventory_cost[g]), price_coef, e.lower_w, e.upper_w};
+  const double offset = -(e.cost_npv + f.inventory_cost[g]);
+  *sc = MmaScalars{offset, offset, price_coef, e.lower_w, e.upper_w, 0.0};
   *rows = make_uint2((uint32_t)(e.lower % f.ring_rows) * (uint32_t)f.row_pitch_bytes, (uint32_t)(e.upper % f.ring_rows) * (uint32_t)f.row_pitch_bytes);
   // gamma may have been written by other CTAs of the same launch: read it through L2
   const double *gl = f.gamma + (size_t)e.lower * f.K, *gu = f.gamma + (size_t)e.upper * f.K;

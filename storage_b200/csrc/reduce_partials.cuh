@@ -10,7 +10,8 @@ namespace lsmc {
 // gamma[g][k] = sum over chunks of partials[g][chunk][k], in a fixed order; one CTA per grid point.
 // mean_mode: gamma[g][0] = sum / total_paths (the sample mean of LSV.cs:181), the other components are zero.
 constexpr int kReduceThreads = 1024;  // stride = 1024 / (acc_k / 2) residue classes: a multiple of 16 for acc_k = 8 and 16
-__device__ __forceinline__ void reduce_partials_body(const ReduceArgs &a) {
+// smem_out != nullptr: the K sums are left in shared memory (first K entries) instead of a.out; the caller synchronises.
+__device__ __forceinline__ void reduce_partials_body(const ReduceArgs &a, double *smem_out = nullptr) {
   const int g = blockIdx.x;
   // This grid point's partial sums are one contiguous run [num_chunks][acc_k].  A thread owns one pair of components
   // (one 16-byte load) of every `stride`-th chunk and keeps eight loads in flight; everything is combined in a fixed order.
@@ -62,7 +63,10 @@ __device__ __forceinline__ void reduce_partials_body(const ReduceArgs &a) {
     for (int run = 0; run < 16; ++run) total += s_run[run][threadIdx.x];
     double out = total;
     if (a.mean_mode) out = (threadIdx.x == 0) ? total / (double)a.total_paths : 0.0;
-    a.out[(size_t)g * a.K + threadIdx.x] = out;
+    if (smem_out)
+      smem_out[threadIdx.x] = out;
+    else
+      a.out[(size_t)g * a.K + threadIdx.x] = out;
   }
 }
 

@@ -22,6 +22,7 @@ import numpy as np
 from . import _abi
 from .errors import (ArgumentException, InvalidOperationException, InventoryConstraintsCannotBeFulfilledException,
                      check_status)
+from .sharding import shard_bounds
 from .time_period import Day
 
 
@@ -450,6 +451,20 @@ class FlatProblem:
         self.first_sim = pb.current_period_is_active
         self.sim_periods = periods[self.first_sim:]
 
+    def signature(self):
+        """Hashable digest of everything lsmc_create reads: two problems with the same signature build the same tables."""
+        import hashlib
+        pb = self.struct
+        m = hashlib.blake2b(digest_size=16)
+        for arr in list(self.flat_storage.arrays.values()) + [self.forward, self.settle_df, self.powers]:
+            m.update(np.ascontiguousarray(arr).tobytes())
+        st = self.flat_storage.struct
+        scalars = (st.num_periods, st.must_be_empty_at_end, st.num_ratchet_rows, tuple(st.terminal_npv_coeff), st.newton_raphson_accuracy,
+                   st.newton_raphson_max_iterations, st.newton_raphson_subdivision,
+                   pb.inventory, pb.current_period_is_active, pb.grid_spacing, pb.numerical_tolerance, pb.extra_decisions, pb.discount_deltas,
+                   pb.simulation_data_returned, pb.num_factors, pb.num_basis, pb.num_sims, pb.reference_compat_terminal_pv)
+        return (m.hexdigest(),) + scalars
+
     def model_arrays(self, model, current):
         """lsmc_multi_factor_params for periods 0..P (vol of the contract delivering in each period, Act/365 times)."""
         F = model.NumFactors
@@ -574,12 +589,63 @@ class Handle:
         return out
 
 
+class PathShard:
+    """This process's share of a valuation whose paths are sharded over several GPUs, one process per GPU (no reference
+    counterpart).  comm_id is the LSMC_COMM_ID_BYTES blob rank 0 drew with lsmc_comm_unique_id and sent to the
+    other ranks by whatever channel the host has (bench.py: torch.distributed broadcast)."""
+
+    def __init__(self, rank, world, comm_id, total_sims):
+        self.rank, self.world, self.comm_id, self.total_sims = int(rank), int(world), bytes(comm_id), int(total_sims)
+        self.begin, self.end = shard_bounds(self.total_sims, self.world, self.rank)
+
+    @property
+    def num_sims(self):
+        return self.end - self.begin
+
+
 class LsmcStorageValuation:
     WithNoLogger = None  # assigned below
 
-    def __init__(self, logger=None, device=0):
+    def __init__(self, logger=None, device=0, shard=None, reuse_handle=False):
+        """shard: PathShard of this process (None: all paths on this GPU).  reuse_handle: keep the device-side state of the
+        last valuation (buffers, tables) and run the next one on it when it has the same problem descriptor; a host that
+        revalues the same storage repeatedly (new simulations, same curves) then pays no table build or device allocation.
+        Call Close() to release it."""
         self._logger = logger
         self._device = device
+        self._shard = shard
+        self._reuse = bool(reuse_handle)
+        self._kept = None  # (signature, Handle)
+
+    def Close(self):
+        if self._kept is not None:
+            self._kept[1].close()
+            self._kept = None
+
+    def __del__(self):
+        try:
+            self.Close()
+        except Exception:
+            pass
+
+    def _handle_for(self, flat):
+        if not self._reuse:
+            return self._open(flat)
+        sig = flat.signature() + (self._device, None if self._shard is None else (self._shard.rank, self._shard.world, self._shard.comm_id))
+        if self._kept is not None and self._kept[0] == sig:
+            self._kept[1].flat = flat
+            return self._kept[1]
+        self.Close()
+        h = self._open(flat)
+        self._kept = (sig, h)
+        return h
+
+    def _open(self, flat):
+        h = Handle(flat, self._device)
+        if self._shard is not None and self._shard.world > 1:
+            s = self._shard
+            h.check(h.lib.lsmc_comm_init(h.h, s.comm_id, s.rank, s.world, s.total_sims))
+        return h
 
     def Calculate(self, lsmcParams, keep_decisions=False, reference_operation_order=False):
         """LsmcStorageValuation.Calculate (LSV.cs:57-657).
@@ -608,12 +674,20 @@ class LsmcStorageValuation:
             return LsmcStorageValuationResults.CreateEndPeriodResults(npv)
 
         spec = p._sim_spec
-        if spec[0] == "panels":
+        shard = self._shard
+        first_path = 0
+        if spec[0] == "panels":  # sharded: the panels hold this rank's slice of the paths
             reg, val = spec[1], spec[2]
             num_sims, num_factors = reg.NumSims, reg.NumFactors
+            if shard is not None and num_sims != shard.num_sims:
+                raise ArgumentException(f"the simulation panels hold {num_sims} paths, this rank's share is {shard.num_sims}")
         else:
             model, num_sims = spec[1], spec[2]
             num_factors = model.NumFactors
+            if shard is not None:
+                if num_sims != shard.total_sims:
+                    raise ArgumentException("PathShard.total_sims differs from the number of simulations of the parameters")
+                num_sims, first_path = shard.num_sims, shard.begin
         flat = FlatProblem(p, num_sims, num_factors, extra_flags=(_abi.LSMC_RETURN_DECISION_INDEX if keep_decisions else 0)
                            | (_abi.LSMC_REFERENCE_OPERATION_ORDER if reference_operation_order else 0))
         if spec[0] == "panels":  # CheckSpotSim (LVP.cs:219-231): host-side, before any device call
@@ -622,7 +696,7 @@ class LsmcStorageValuation:
                 for sp in flat.sim_periods:
                     if sp not in have:
                         raise ArgumentException(f"{name} does not contain simulations for period {sp}.")
-        h = Handle(flat, self._device)
+        h = self._handle_for(flat)
         try:
             lib = h.lib
             if spec[0] == "panels":
@@ -632,8 +706,8 @@ class LsmcStorageValuation:
             else:
                 _, model, _, seed, val_seed, antithetic = spec
                 mp, keep = flat.model_arrays(model, p.CurrentPeriod)
-                h.check(lib.lsmc_simulate(h.h, 0, C.byref(mp), seed, int(antithetic), 0))
-                h.check(lib.lsmc_simulate(h.h, 1, C.byref(mp), val_seed, int(antithetic), 0))
+                h.check(lib.lsmc_simulate(h.h, 0, C.byref(mp), seed, int(antithetic), first_path))
+                h.check(lib.lsmc_simulate(h.h, 1, C.byref(mp), val_seed, int(antithetic), first_path))
                 del keep
             cancel = C.c_int(0)
             token = p.CancellationToken
@@ -649,7 +723,8 @@ class LsmcStorageValuation:
             h.check(lib.lsmc_run(h.h, C.cast(cb, C.c_void_p), None, C.addressof(cancel)))
             return self._collect(h, flat, p, num_sims, num_factors, keep_decisions)
         finally:
-            h.close()
+            if not self._reuse:
+                h.close()
 
     @staticmethod
     def _collect(h, flat, p, num_sims, num_factors, keep_decisions):
