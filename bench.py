@@ -233,6 +233,10 @@ def run_gpu(args):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: storage_b200 has no CPU fallback")
+    # rank 0 prints exactly ONE line on stdout: anything a library writes there meanwhile (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
@@ -444,7 +448,8 @@ def run_gpu(args):
     if not args.no_cpu_baseline and world == 1:
         base, _, _ = cpu_baseline(CONFIGS[args.config], args.cpu_sims)
         out["cpu_baseline"] = base
-    print(json.dumps(out))
+    sys.stdout.flush()
+    os.write(real_stdout, (json.dumps(out) + "\n").encode())
     if dist:
         dist.destroy_process_group()
 

@@ -54,6 +54,12 @@ struct BackwardStepArgs {
   const double *q_prev; // [K][pitch] basis rows of period-1 for the regression sums (NULL with accumulate: mean mode)
   int accumulate;       // 0: no further regression (period 0)
   double *partials;     // [G][num_tiles][acc] per-tile sums of q_prev[k] * v_this[g] (num_tiles = gridDim.y)
+  // FP64-mma sweep kernel: first level of the reduction of the per-tile sums inside the kernel.  The CTA that is last to finish
+  // among the group_tiles path tiles of a group adds the group's sums in tile order (deterministic) into group_partials
+  // [G][num_groups][acc]; the per-step reduction kernel then reads 1/group_tiles of the data.  0: off.
+  double *group_partials;
+  unsigned int *group_counters;  // [gridDim.x][num_groups], zero between launches
+  int group_tiles;
   int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring and sweep kernels)
   const SweepBlock *sweep_blocks;  // row-ring sweep kernel: [blocks of 8 grid points] of this period
   const void *point_tables;  // sweep kernel: [G] per-grid-point records written by fold_tables_kernel

@@ -187,6 +187,8 @@ struct lsmc_handle {
   DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
   DeviceBuffer<unsigned int> fold_counter;  // device-wide arrival counter of reduce_fold_kernel (self-resetting)
+  DeviceBuffer<double> group_partials;      // FP64-mma sweep kernel: sums of groups of kGroupTiles path tiles (BackwardStepArgs)
+  DeviceBuffer<unsigned int> group_counters;
   std::vector<size_t> window_offset;  // per period: first block in sweep_blocks
   std::vector<int> sweep_ring_rows;   // per period: ring size of the row-ring sweep kernel (0: direct-load sweep kernel)
   DeviceBuffer<SweepBlock> sweep_blocks;  // [window_offset[p] + block] row windows of the row-ring sweep kernel
@@ -647,6 +649,11 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     f.out = h->point_tables.ptr;
     return f;
   };
+  struct StepSums {  // where a step left its regression partial sums, and how many chunks per grid point
+    const double *partials;
+    int chunks;
+  };
+  constexpr int kGroupTiles = 32;
   auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this, bool fold_done) {
     const PeriodTables &pt = h->tables.periods[p];
     if (has_basis(p - 1)) cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0);
@@ -707,7 +714,15 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     }
     mark(p, 3);
     if (!terminal && time_steps) cudaEventRecord(step_events[2 * p], st);
+    StepSums out{h->partials.ptr, (int)tiles};
     if (sweep && h->use_mma && a.ring_rows > 0) {
+      static const bool group_reduce = [] { const char *e = std::getenv("LSMC_GROUP_REDUCE"); return !(e && e[0] == '0'); }();  // test hook
+      if (group_reduce && tiles > 2 * kGroupTiles) {
+        a.group_partials = h->group_partials.ptr;
+        a.group_counters = h->group_counters.ptr;
+        a.group_tiles = kGroupTiles;
+        out = StepSums{h->group_partials.ptr, (int)((tiles + kGroupTiles - 1) / kGroupTiles)};
+      }
       launch_backward_sweep_mma(a, gsplit, tiles, st);
     } else if (sweep) {
       launch_backward_sweep(a, gsplit, tiles, st);
@@ -723,15 +738,15 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       cudaStreamWaitEvent(h->aux_stream, h->ev_step[p % 3], 0);
       launch_basis_for(p - 3);
     }
-    return (int)tiles;
+    return out;
   };
-  auto reduce_gamma = [&](int p, int G_next, int num_chunks) -> bool {  // true: the point tables of step p were folded as well
+  auto reduce_gamma = [&](int p, int G_next, StepSums sums) -> bool {  // true: the point tables of step p were folded as well
     // regression coefficients of V_{p+1} on period p's basis (LSV.cs:199-212) from the partial sums the kernel that
     // produced V_{p+1} left behind
     const bool mean_mode = (p == 0 && h->current_active);
     ReduceArgs r{};
-    r.partials = h->partials.ptr;
-    r.num_chunks = num_chunks;
+    r.partials = sums.partials;
+    r.num_chunks = sums.chunks;
     r.G = G_next;
     r.K = K;
     r.acc_k = h->acc_k;
@@ -772,7 +787,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
 
   double *v_next = h->v_a.ptr, *v_this = h->v_b.ptr;
   const auto enqueue0 = std::chrono::steady_clock::now();
-  int chunks = launch_step(P, true, nullptr, v_next, false);
+  StepSums chunks = launch_step(P, true, nullptr, v_next, false);
   const double back_step = 0.66 / P;  // BackwardPcntTime (LSV.cs:48,164)
   double prog = 0.0;
   for (int p = P - 1; p >= 0; --p) {
@@ -1054,6 +1069,12 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
                                       (size_t)((h->Gmax + 7) / 8) * mma_block_record_bytes(h->K)) / sizeof(double));
     h->fold_counter.allocate(1);
     CUDA_OK(cudaMemset(h->fold_counter.ptr, 0, sizeof(unsigned int)));
+    {
+      const size_t groups = (size_t)(num_tiles + 31) / 32;
+      h->group_partials.allocate(groups * h->Gmax * h->acc_k);
+      h->group_counters.allocate(groups * ((h->Gmax + 7) / 8));
+      CUDA_OK(cudaMemset(h->group_counters.ptr, 0, h->group_counters.count * sizeof(unsigned int)));
+    }
     h->qbuf[0].allocate((size_t)h->K * h->pitch);
     h->qbuf[1].allocate((size_t)h->K * h->pitch);
     h->qbuf[2].allocate((size_t)h->K * h->pitch);
