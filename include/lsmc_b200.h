@@ -256,7 +256,9 @@ lsmc_status lsmc_simulate(lsmc_handle *h, int which, const lsmc_multi_factor_par
  * clearing): calls whose GPU work overlaps, on different streams or from different host threads, corrupt each other's
  * table and must be serialised by the caller.  The first call on a device looks up the array's device address; make that
  * first call before starting any stream capture.  The kernel runs on `cuda_stream` (a cudaStream_t, NULL = default
- * stream) and the call returns after it has finished.  Errors: message via lsmc_last_error(NULL). */
+ * stream); the call waits for it (it synchronises that stream) and returns after it has finished.  `device` is made current
+ * for the duration of the call and the caller's current device is put back before it returns.  Errors: message via
+ * lsmc_last_error(NULL). */
 lsmc_status lsmc_simulate_noalloc(int device, const lsmc_multi_factor_params *params, int32_t num_periods,
                                   int32_t current_period_is_active, const double *forward_price, int64_t num_sims, uint64_t seed,
                                   int antithetic, int64_t first_path_id, double *spot_device, double *const *factors_device,

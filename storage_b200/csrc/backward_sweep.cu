@@ -784,10 +784,10 @@ __global__ void __launch_bounds__(kRingThreads, LSMC_RING_MIN_CTAS) backward_swe
 template <int KP>
 void launch_sweep_ring_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
   if (a.fused_payoff) {
-    cudaFuncSetAttribute(backward_sweep_ring_kernel<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dynamic_smem<backward_sweep_ring_kernel<KP, true>>(smem);
     backward_sweep_ring_kernel<KP, true><<<grid, kRingThreads, smem, stream>>>(a);
   } else {
-    cudaFuncSetAttribute(backward_sweep_ring_kernel<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dynamic_smem<backward_sweep_ring_kernel<KP, false>>(smem);
     backward_sweep_ring_kernel<KP, false><<<grid, kRingThreads, smem, stream>>>(a);
   }
 }
@@ -795,10 +795,10 @@ void launch_sweep_ring_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, 
 template <int KP>
 void launch_sweep_for_k(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
   if (a.fused_payoff) {
-    if (smem > 48 * 1024) cudaFuncSetAttribute(backward_sweep_kernel<KP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dynamic_smem<backward_sweep_kernel<KP, true>>(smem);
     backward_sweep_kernel<KP, true><<<grid, kSweepThreads, smem, stream>>>(a);
   } else {
-    if (smem > 48 * 1024) cudaFuncSetAttribute(backward_sweep_kernel<KP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    ensure_dynamic_smem<backward_sweep_kernel<KP, false>>(smem);
     backward_sweep_kernel<KP, false><<<grid, kSweepThreads, smem, stream>>>(a);
   }
 }

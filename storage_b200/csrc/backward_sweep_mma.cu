@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
 
 template <int KSTEPS, int MB>
 void launch_mma(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
-  cudaFuncSetAttribute(backward_sweep_mma_kernel<KSTEPS, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  ensure_dynamic_smem<backward_sweep_mma_kernel<KSTEPS, MB>>(smem);
   backward_sweep_mma_kernel<KSTEPS, MB><<<grid, kMmaThreads, smem, stream>>>(a);
 }
 

@@ -959,15 +959,15 @@ void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t sme
       if (static_cast<const BackwardStepArgs *>(args)->D == 3) {
         const BackwardStepArgs &ba = *static_cast<const BackwardStepArgs *>(args);
         if (ba.fused_payoff && !ba.terminal_mode) {
-          if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+          ensure_dynamic_smem<backward_step_kernel<KP, 3, true>>(smem);
           backward_step_kernel<KP, 3, true><<<grid, block, smem, stream>>>(ba);
         } else {
-          if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+          ensure_dynamic_smem<backward_step_kernel<KP, 3, false>>(smem);
           backward_step_kernel<KP, 3, false><<<grid, block, smem, stream>>>(ba);
         }
         break;
       }
-      if (smem > 48 * 1024) cudaFuncSetAttribute(backward_step_kernel<KP, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      ensure_dynamic_smem<backward_step_kernel<KP, 0, false>>(smem);
       {
         static int carve = -2;
         if (carve == -2) { const char *e = getenv("LSMC_CARVEOUT"); carve = e ? atoi(e) : -1; }
@@ -979,7 +979,7 @@ void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t sme
       basis_kernel<KP><<<grid, block, 0, stream>>>(*static_cast<const BasisArgs *>(args));
       break;
     case 3:
-      if (smem > 48 * 1024) cudaFuncSetAttribute(forward_kernel<KP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      ensure_dynamic_smem<forward_kernel<KP>>(smem);
       forward_kernel<KP><<<grid, block, smem, stream>>>(*static_cast<const ForwardArgs *>(args));
       break;
   }

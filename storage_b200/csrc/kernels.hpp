@@ -2,8 +2,11 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstddef>
 #include <cstdint>
+#include <stdexcept>
+#include <string>
 
 #include "device_types.hpp"
 
@@ -75,6 +78,23 @@ struct XchgArgs {
 constexpr size_t kXchgFlagStride = 128;
 __host__ __device__ inline size_t xchg_data_offset(int world) { return ((size_t)world * kXchgFlagStride + 255) / 256 * 256; }
 __host__ __device__ inline size_t xchg_buffer_bytes(int world, size_t capacity) { return xchg_data_offset(world) + 2 * (size_t)world * capacity * sizeof(double); }
+
+// Raises a kernel's dynamic shared-memory limit, once per device and size (the attribute is sticky; setting it on every
+// launch costs host time in the per-step loop), and reports a refusal instead of letting the launch fail later.
+template <auto Kernel>
+inline void ensure_dynamic_smem(size_t smem) {
+  if (smem <= 48 * 1024) return;
+  constexpr int kDevices = 64;
+  static std::atomic<size_t> granted[kDevices] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const bool tracked = dev >= 0 && dev < kDevices;
+  if (tracked && granted[dev].load(std::memory_order_relaxed) >= smem) return;
+  const cudaError_t e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess)
+    throw std::runtime_error(std::string("cudaFuncSetAttribute(MaxDynamicSharedMemorySize = ") + std::to_string(smem) + ") failed: " + cudaGetErrorString(e));
+  if (tracked) granted[dev].store(smem, std::memory_order_relaxed);
+}
 
 int padded_basis(int K);
 inline int acc_width(int K) { return padded_basis(K) <= 8 ? 8 : 16; }

@@ -180,6 +180,8 @@ struct lsmc_handle {
   PinnedStager stager;                         // pinned double buffer for whole-panel host <-> device copies
   cudaStream_t aux_stream = nullptr;          // basis rows of period p-3 are materialised here while step p-1 runs
   cudaEvent_t ev_basis[3] = {}, ev_step[3] = {}, ev_prepass = nullptr;
+  std::vector<cudaEvent_t> step_events;  // two timing events per backward step, created once and kept for later runs
+  cudaEvent_t ev_window[3] = {};        // completion of a window of backward steps: progress reports and cancellation follow the GPU
   SimSet sims[2];
   DeviceBuffer<double> v_a, v_b, grids, gamma, rinv, partials, gram_partials, inv_cost, pv, final_inv, step_sums, step_totals,
       block_sums, gather_buf, qbuf[3], ratchet_inv, ratchet_min, ratchet_max, ratchet_min_slope, ratchet_max_slope, poly_min, poly_max;
@@ -536,14 +538,21 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   Timer t_pinv(st), t_back(st), t_fwd(st), t_dev(st);
   struct EventList {
     std::vector<cudaEvent_t> ev;
-    explicit EventList(size_t n) : ev(n) {
-      for (auto &e : ev) cudaEventCreate(&e);
+    explicit EventList(size_t n) : ev(n, nullptr) {
+      for (auto &e : ev) CUDA_OK(cudaEventCreate(&e));
     }
     ~EventList() {
-      for (auto &e : ev) cudaEventDestroy(e);
+      for (auto &e : ev)
+        if (e) cudaEventDestroy(e);
     }
     cudaEvent_t &operator[](size_t i) { return ev[i]; }
-  } step_events(2 * (size_t)P);
+  };
+  std::vector<cudaEvent_t> &step_events = h->step_events;
+  while (step_events.size() < 2 * (size_t)P) {
+    cudaEvent_t e = nullptr;
+    CUDA_OK(cudaEventCreate(&e));
+    step_events.push_back(e);
+  }
   t_dev.start();
   // ---- regression pre-pass: Gram matrices, Cholesky factors and R^-1 of every regression period (LSV.cs:191-196)
   const int first_reg = h->current_active ? 1 : 0;
@@ -592,11 +601,16 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   t_back.start();
   const int64_t num_tiles = (N + kTilePaths - 1) / kTilePaths;
   int sm_count = 148;
-  cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device);
+  CUDA_OK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device));
   const bool time_steps = std::getenv("LSMC_NO_STEP_EVENTS") == nullptr;
   const bool trace = std::getenv("LSMC_TRACE") != nullptr;
   EventList tr(trace ? 5 * (size_t)(P + 1) : 0);
-  auto mark = [&](int p, int i) { if (trace) cudaEventRecord(tr[5 * (size_t)p + i], st); };
+  auto mark = [&](int p, int i) { if (trace) CUDA_OK(cudaEventRecord(tr[5 * (size_t)p + i], st)); };
+  // a launch that could not be enqueued (bad configuration, sticky error) is reported with its kernel and period
+  auto launched = [&](const char *what, int p) {
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) throw CudaFailure(std::string(what) + " (period " + std::to_string(p) + ") could not be launched: " + cudaGetErrorString(e));
+  };
   const bool use_sweep = [] { const char *e = std::getenv("LSMC_SWEEP"); return !(e && e[0] == '0'); }();  // test hook: 0 = general kernel
   auto q_buffer = [&](int period) { return h->qbuf[period % 3].ptr; };
   auto has_basis = [&](int period) { return period >= first_reg && period < P; };
@@ -611,7 +625,8 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     b.powers = h->d_powers.ptr;
     b.q_out = q_buffer(period);
     launch_basis(b, h->aux_stream);
-    cudaEventRecord(h->ev_basis[period % 3], h->aux_stream);
+    launched("basis_kernel", period);
+    CUDA_OK(cudaEventRecord(h->ev_basis[period % 3], h->aux_stream));
     launches++;
     if (debug_sync) {
       cudaError_t e = cudaStreamSynchronize(h->aux_stream);
@@ -624,8 +639,8 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   // more than it hides; as it is, the basis kernel fills the SMs the small reduction and fold kernels leave idle):
   // step p reads q(p) and q(p-1); once it has finished, the buffer of q(p) is free for q(p-3), which is then computed while
   // step p-1 runs and is first needed by step p-2.
-  cudaEventRecord(h->ev_prepass, st);
-  cudaStreamWaitEvent(h->aux_stream, h->ev_prepass, 0);
+  CUDA_OK(cudaEventRecord(h->ev_prepass, st));
+  CUDA_OK(cudaStreamWaitEvent(h->aux_stream, h->ev_prepass, 0));
   if (has_basis(P - 1)) launch_basis_for(P - 1);
   if (has_basis(P - 2)) launch_basis_for(P - 2);
   auto uses_sweep = [&](int p) { return D == 3 && use_sweep; };
@@ -656,7 +671,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   constexpr int kGroupTiles = 32;
   auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this, bool fold_done) {
     const PeriodTables &pt = h->tables.periods[p];
-    if (has_basis(p - 1)) cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0);
+    if (has_basis(p - 1)) CUDA_OK(cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0));
     BackwardStepArgs a{};
     a.N = N;
     a.pitch = h->pitch;
@@ -713,7 +728,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       a.sweep_blocks = h->sweep_blocks.ptr + h->window_offset[p];
     }
     mark(p, 3);
-    if (!terminal && time_steps) cudaEventRecord(step_events[2 * p], st);
+    if (!terminal && time_steps) CUDA_OK(cudaEventRecord(step_events[2 * p], st));
     StepSums out{h->partials.ptr, (int)tiles};
     if (sweep && h->use_mma && a.ring_rows > 0) {
       static const bool group_reduce = [] { const char *e = std::getenv("LSMC_GROUP_REDUCE"); return !(e && e[0] == '0'); }();  // test hook
@@ -729,13 +744,14 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     } else {
       launch_backward_step(a, gsplit, num_tiles, st);
     }
-    if (!terminal && time_steps) cudaEventRecord(step_events[2 * p + 1], st);
+    launched(sweep ? "backward sweep kernel" : "backward_step_kernel", p);
+    if (!terminal && time_steps) CUDA_OK(cudaEventRecord(step_events[2 * p + 1], st));
     mark(p, 4);
     launches++;
     dbg(sweep ? "backward_sweep_kernel" : "backward_step_kernel", p);
     if (has_basis(p - 3)) {
-      cudaEventRecord(h->ev_step[p % 3], st);
-      cudaStreamWaitEvent(h->aux_stream, h->ev_step[p % 3], 0);
+      CUDA_OK(cudaEventRecord(h->ev_step[p % 3], st));
+      CUDA_OK(cudaStreamWaitEvent(h->aux_stream, h->ev_step[p % 3], 0));
       launch_basis_for(p - 3);
     }
     return out;
@@ -790,14 +806,31 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   StepSums chunks = launch_step(P, true, nullptr, v_next, false);
   const double back_step = 0.66 / P;  // BackwardPcntTime (LSV.cs:48,164)
   double prog = 0.0;
-  for (int p = P - 1; p >= 0; --p) {
+  // Steps are enqueued in windows; a window's progress notifications (one per step, as the reference gives them) and the
+  // cancellation poll happen when the GPU has FINISHED that window, two windows behind the enqueueing, so that the GPU always
+  // has at least one whole window queued while the host waits.
+  constexpr int kWindow = 64, kWindowsInFlight = 2;
+  int windows_enqueued = 0, windows_reported = 0;
+  auto report_window = [&](int w) {  // blocks until window w is done on the GPU
+    CUDA_OK(cudaEventSynchronize(h->ev_window[w % 3]));
+    const int first = P - 1 - w * kWindow, last = std::max(first - kWindow + 1, 0);
+    for (int q = first; q >= last; --q) {
+      prog += back_step;
+      if (progress) progress(prog, user);
+    }
     check_cancel();
+  };
+  for (int p = P - 1; p >= 0; --p) {
     mark(p, 0);
     const bool folded = reduce_gamma(p, (int)h->tables.periods[p + 1].grid.size(), chunks);
+    launched("per-step reduction", p);
     chunks = launch_step(p, false, v_next, v_this, folded);
     std::swap(v_next, v_this);
-    prog += back_step;
-    if (progress) progress(prog, user);
+    if ((P - 1 - p) % kWindow == kWindow - 1 || p == 0) {
+      CUDA_OK(cudaEventRecord(h->ev_window[windows_enqueued % 3], st));
+      ++windows_enqueued;
+      while (windows_enqueued - windows_reported > kWindowsInFlight) report_window(windows_reported++);
+    }
   }
   const double *v_first = v_next;  // storage value by sim at period 0
   if (trace) {
@@ -813,7 +846,6 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     std::fprintf(stderr, "[lsmc] backward induction: %d steps enqueued in %.3f ms of host time\n", P,
                  std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - enqueue0).count());
   t_back.stop();
-  check_cancel();
 
   // ---- forward simulation (LSV.cs:390-521)
   t_fwd.start();
@@ -863,7 +895,10 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.error_flag = h->error_flag.ptr;
   fa.snapped = reinterpret_cast<unsigned long long *>(h->error_flag.ptr + 2);
   launch_forward(fa, fwd_ctas, st);
+  launched("forward_kernel", -1);
   launches++;
+  // the forward pass is queued behind the last windows: report those while it runs
+  while (windows_reported < windows_enqueued) report_window(windows_reported++);
   dbg("forward_kernel", -1);
   launch_reduce_step_sums(h->step_sums.ptr, P, fwd_ctas, sums_width, h->step_totals.ptr, st);
   launches++;
@@ -1050,6 +1085,7 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     CUDA_OK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
     for (auto &e : h->ev_basis) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     for (auto &e : h->ev_step) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto &e : h->ev_window) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CUDA_OK(cudaEventCreateWithFlags(&h->ev_prepass, cudaEventDisableTiming));
     h->v_a.allocate((size_t)h->Gmax * h->pitch);
     h->v_b.allocate((size_t)h->Gmax * h->pitch);
@@ -1291,6 +1327,8 @@ void lsmc_destroy(lsmc_handle *h) {
     if (h->aux_stream) cudaStreamDestroy(h->aux_stream);
     for (auto &e : h->ev_basis) if (e) cudaEventDestroy(e);
     for (auto &e : h->ev_step) if (e) cudaEventDestroy(e);
+    for (auto &e : h->ev_window) if (e) cudaEventDestroy(e);
+    for (auto &e : h->step_events) if (e) cudaEventDestroy(e);
     if (h->ev_prepass) cudaEventDestroy(h->ev_prepass);
   }
   delete h;
