@@ -72,6 +72,10 @@ enum {
                                                reference's own sequence of roundings (LSV.cs:317-336) instead of the fused
                                                form S*coef + offset; both are within 1e-9 of the reference, the fused one is
                                                the default because it needs a third fewer FP64 operations */
+  LSMC_STREAM_PANELS = 1 << 18, /* no reference counterpart: do not keep the requested per-simulation result panels on the device
+                                   (6 x (P+1) x N doubles: 88 GB at 1M paths x 1825 periods); run the forward simulation in blocks
+                                   of periods and deliver every finished block to the host arrays registered with
+                                   lsmc_set_panel_sink while the next block is computed */
   LSMC_RETURN_ALL = 1 | (1 << 2) | (1 << 3) | (1 << 4) | (1 << 5) | (1 << 6) | (1 << 7) | (1 << 8) | (1 << 9) | (1 << 10)
 };
 
@@ -198,6 +202,7 @@ typedef struct lsmc_results {
      inventory had left [MinInventory, MaxInventory] by less than NumericalTolerance and was moved onto the limit, where the
      reference throws (CmdtyStorage.cs:88-94).  0 means the run never relied on the departure. */
   int64_t snapped_inventories;
+  double ms_upload; /* host wall time spent staging caller-supplied simulation panels to the device (lsmc_set_sims, lsmc_set_sims_async) */
 } lsmc_results;
 
 /* Per-sim panels selectable with SimulationDataReturned (LSV.cs:356-366,636-643). */
@@ -237,6 +242,18 @@ lsmc_status lsmc_set_sims(lsmc_handle *h, int which, const double *spot, const d
 /* Same, for simulations already resident in device memory (device pointers, same layout).  The
  * handle keeps the pointers: the buffers must stay valid until lsmc_run returns. */
 lsmc_status lsmc_set_sims_device(lsmc_handle *h, int which, const double *spot, const double *const *factors);
+
+/* lsmc_set_sims without the wait (the caller-supplied-simulation overload at production size moves 58 GB per set):
+ * returns at once, the panels are staged to the device by a worker of the handle.  The arrays must stay valid and unchanged
+ * until lsmc_run has returned.  lsmc_run waits for the regression set before its first kernel and for the valuation set before
+ * the forward simulation, so a valuation set given this way is uploaded while the backward induction runs. */
+lsmc_status lsmc_set_sims_async(lsmc_handle *h, int which, const double *spot, const double *const *factors);
+
+/* With LSMC_STREAM_PANELS (LsmcStorageValuation.cs:356-377,492-507,636-643 at sizes whose panels do not fit on the device):
+ * where lsmc_run delivers panel `which` (LSMC_PANEL_INVENTORY .. LSMC_PANEL_PV, LSMC_PANEL_DECISION_INDEX), a host array of the
+ * shape lsmc_copy_panel documents.  Must be called for every requested panel before lsmc_run; the array must stay valid until
+ * lsmc_run has returned.  lsmc_copy_panel is not available for streamed panels. */
+lsmc_status lsmc_set_panel_sink(lsmc_handle *h, lsmc_panel which, double *host_destination);
 
 /* Replaces SimulateWithMultiFactorModelAndMersenneTwister (LVP.cs:185-196,164-183): simulate on the
  * device.  Counter-based RNG keyed by (seed, global path id, period) so a path's draws do not depend

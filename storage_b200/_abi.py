@@ -24,6 +24,7 @@ LSMC_COMM_ID_BYTES = 128
 
 LSMC_RETURN_DECISION_INDEX = 1 << 16
 LSMC_REFERENCE_OPERATION_ORDER = 1 << 17
+LSMC_STREAM_PANELS = 1 << 18
 
 c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)
@@ -125,6 +126,7 @@ class lsmc_results(C.Structure):
         ("backward_kernel_launches", C.c_int64),
         ("ms_device", C.c_double),
         ("snapped_inventories", C.c_int64),
+        ("ms_upload", C.c_double),
     ]
 
 
@@ -139,6 +141,8 @@ SYMBOLS = [
     ("lsmc_create", C.c_int, [C.POINTER(lsmc_problem), C.c_int, C.POINTER(_H)]),
     ("lsmc_set_sims", C.c_int, [_H, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
     ("lsmc_set_sims_device", C.c_int, [_H, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
+    ("lsmc_set_sims_async", C.c_int, [_H, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
+    ("lsmc_set_panel_sink", C.c_int, [_H, C.c_int, C.c_void_p]),
     ("lsmc_simulate", C.c_int, [_H, C.c_int, C.POINTER(lsmc_multi_factor_params), C.c_uint64, C.c_int, C.c_int64]),
     ("lsmc_simulate_noalloc", C.c_int,
      [C.c_int, C.POINTER(lsmc_multi_factor_params), C.c_int32, C.c_int32, c_double_p, C.c_int64, C.c_uint64, C.c_int, C.c_int64,

@@ -272,45 +272,6 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     mbar_wait(&s_gemm[bl & 1], (bl >> 1) & 1);
     combine(bl);
   }
-  if (a.accumulate && a.group_tiles > 0) {
-    // first level of the cross-tile reduction: the last CTA of this tile group to get here adds the group's sums, in tile order
-    __shared__ bool s_last;
-    const int gt = a.group_tiles;
-    const int num_groups = ((int)gridDim.y + gt - 1) / gt;
-    const int group = (int)tile / gt, first = group * gt, members = min(gt, (int)gridDim.y - first);
-    unsigned int *counter = a.group_counters + (size_t)blockIdx.x * num_groups + group;
-    __threadfence();  // this CTA's sums are visible device-wide before it is counted
-    __syncthreads();
-    if (threadIdx.x == 0) s_last = atomicAdd(counter, 1u) == (unsigned)(members - 1);
-    __syncthreads();
-    if (s_last) {
-      __threadfence();
-      constexpr int PAIRS = ACC / 2;
-      for (int item = threadIdx.x; item < glimit * PAIRS; item += kMmaThreads) {
-        const int g = item / PAIRS, kp = item - g * PAIRS;
-        const double2 *src = reinterpret_cast<const double2 *>(a.partials + ((size_t)(gbeg + g) * gridDim.y + first) * ACC) + kp;
-        double2 sum = make_double2(0.0, 0.0);
-        int t = 0;
-        for (; t + 8 <= members; t += 8) {  // eight loads in flight, added in tile order
-          double2 v[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = __ldcg(src + (size_t)(t + i) * PAIRS);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            sum.x += v[i].x;
-            sum.y += v[i].y;
-          }
-        }
-        for (; t < members; ++t) {
-          const double2 v = __ldcg(src + (size_t)t * PAIRS);
-          sum.x += v.x;
-          sum.y += v.y;
-        }
-        reinterpret_cast<double2 *>(a.group_partials + ((size_t)(gbeg + g) * num_groups + group) * ACC)[kp] = sum;
-      }
-      if (threadIdx.x == 0) *counter = 0u;  // ready for the next launch
-    }
-  }
 }
 
 template <int KSTEPS, int MB>

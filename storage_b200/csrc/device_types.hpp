@@ -54,12 +54,6 @@ struct BackwardStepArgs {
   const double *q_prev; // [K][pitch] basis rows of period-1 for the regression sums (NULL with accumulate: mean mode)
   int accumulate;       // 0: no further regression (period 0)
   double *partials;     // [G][num_tiles][acc] per-tile sums of q_prev[k] * v_this[g] (num_tiles = gridDim.y)
-  // FP64-mma sweep kernel: first level of the reduction of the per-tile sums inside the kernel.  The CTA that is last to finish
-  // among the group_tiles path tiles of a group adds the group's sums in tile order (deterministic) into group_partials
-  // [G][num_groups][acc]; the per-step reduction kernel then reads 1/group_tiles of the data.  0: off.
-  double *group_partials;
-  unsigned int *group_counters;  // [gridDim.x][num_groups], zero between launches
-  int group_tiles;
   int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring and sweep kernels)
   const SweepBlock *sweep_blocks;  // row-ring sweep kernel: [blocks of 8 grid points] of this period
   const void *point_tables;  // sweep kernel: [G] per-grid-point records written by fold_tables_kernel
@@ -89,6 +83,10 @@ constexpr int kForwardSums = 8;  // sum_spot_vol, sum_vol, sum_cons, sum_loss, s
 struct ForwardArgs {
   int64_t N;
   int P, K, F, Gmax;
+  // Periods [p_begin, p_end) of the forward simulation in this launch.  A launch that does not start at period 0 resumes from
+  // the per-path state (inventory, PV so far) the previous launch left in final_inventory / pv_by_sim; panel rows are written
+  // relative to panel_row0 (streamed panels: the launch's first period; resident panels: 0).
+  int p_begin, p_end, panel_row0;
   int64_t sim_pitch;               // N (caller layout)
   const DevPeriodParams *periods;  // [P]
   const double *ratchet_inventory, *ratchet_min, *ratchet_max;

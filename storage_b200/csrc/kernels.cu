@@ -734,13 +734,15 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
   // carries from one period to the next (inventory, PV so far) waits in shared memory.
   const int64_t num_tiles = (a.N + kThreads - 1) / kThreads;
   for (int t = 0; t < a.tiles_per_cta; ++t) {
-    s_inv[t * kThreads + threadIdx.x] = a.start_inventory;
-    s_pv[t * kThreads + threadIdx.x] = 0.0;
+    const int64_t n = (blockIdx.x + (int64_t)t * gridDim.x) * kThreads + threadIdx.x;
+    const bool resume = a.p_begin > 0 && n < a.N;
+    s_inv[t * kThreads + threadIdx.x] = resume ? a.final_inventory[n] : a.start_inventory;
+    s_pv[t * kThreads + threadIdx.x] = resume ? a.pv_by_sim[n] : 0.0;
   }
   int err = 0;
   unsigned long long snapped = 0;  // inventories moved onto a limit (lsmc_results.snapped_inventories)
 
-  for (int p = 0; p < a.P; ++p) {
+  for (int p = a.p_begin; p < a.p_end; ++p) {
     __syncthreads();  // previous period's shared tables are no longer in use
     if (threadIdx.x == 0) s_pp = a.periods[p];
     __syncthreads();
@@ -845,7 +847,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
       const double next_inventory = inventory + best_volume - loss;  // LSV.cs:485
 
       if (valid) {
-        const size_t off = (size_t)p * a.N + n;
+        const size_t off = (size_t)(p - a.panel_row0) * a.N + n;
         if (a.p_inventory) a.p_inventory[off] = inventory;
         if (a.p_volume) a.p_volume[off] = best_volume;
         if (a.p_consumed) a.p_consumed[off] = best_consumed;
@@ -895,7 +897,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
       const double inventory = s_inv[t * kThreads + threadIdx.x];
       a.pv_by_sim[n] = s_pv[t * kThreads + threadIdx.x];
       a.final_inventory[n] = inventory;
-      if (a.p_inventory) a.p_inventory[(size_t)a.P * a.N + n] = inventory;
+      if (a.p_inventory && a.p_end == a.P && a.panel_row0 == 0) a.p_inventory[(size_t)a.P * a.N + n] = inventory;
     }
   }
   if (err) atomicExch(a.error_flag, err);

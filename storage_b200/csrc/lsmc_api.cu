@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstdio>
 #include <cstring>
+#include <exception>
 #include <memory>
 #include <string>
 #include <thread>
@@ -152,6 +153,25 @@ struct SimSet {
   DeviceBuffer<double> owned_spot;
   DeviceBuffer<double> owned_factors[LSMC_MAX_FACTORS];
   double ms_simulation = 0.0;
+  double ms_upload = 0.0;  // host wall time of staging the caller's panels to the device
+  // lsmc_set_sims_async: the panels travel on a worker thread with its own stream and pinned staging while the caller goes on
+  // (the valuation simulations are not needed before the forward pass: their upload overlaps the backward induction)
+  std::thread uploader;
+  std::exception_ptr upload_error;
+  std::unique_ptr<PinnedStager> upload_stager;
+  cudaStream_t upload_stream = nullptr;
+  void wait_upload() {  // joins the worker; rethrows what it threw
+    if (uploader.joinable()) uploader.join();
+    if (upload_error) {
+      std::exception_ptr e = upload_error;
+      upload_error = nullptr;
+      std::rethrow_exception(e);
+    }
+  }
+  ~SimSet() {
+    if (uploader.joinable()) uploader.join();
+    if (upload_stream) cudaStreamDestroy(upload_stream);
+  }
 };
 
 }  // namespace
@@ -189,14 +209,20 @@ struct lsmc_handle {
   DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
   DeviceBuffer<unsigned int> fold_counter;  // device-wide arrival counter of reduce_fold_kernel (self-resetting)
-  DeviceBuffer<double> group_partials;      // FP64-mma sweep kernel: sums of groups of kGroupTiles path tiles (BackwardStepArgs)
-  DeviceBuffer<unsigned int> group_counters;
   std::vector<size_t> window_offset;  // per period: first block in sweep_blocks
   std::vector<int> sweep_ring_rows;   // per period: ring size of the row-ring sweep kernel (0: direct-load sweep kernel)
   DeviceBuffer<SweepBlock> sweep_blocks;  // [window_offset[p] + block] row windows of the row-ring sweep kernel
   DeviceBuffer<DevPeriodParams> period_params;
   DeviceBuffer<BasisSpec> gram_specs;
   DeviceBuffer<double> panels[7];  // inventory, volume, consumed, loss, net volume, pv, decision index
+  // LSMC_STREAM_PANELS: the panels above are rings of 2 x stream_block periods; the forward simulation runs block by block and
+  // every finished block is copied into the caller's host arrays (panel sinks) while the next one is computed
+  bool stream_panels = false;
+  int stream_block = 0;
+  double *sinks[7] = {};
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_block[2] = {}, ev_copied[2] = {};
+  PinnedStager sink_stager;
   std::vector<size_t> table_offset;  // per period: first grid point in the concatenated tables
 
   Comm comm;  // single rank unless lsmc_comm_init was called
@@ -508,6 +534,8 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   const int P = h->P, K = h->K, F = h->F, D = h->D, Gmax = h->Gmax;
   const int64_t N = h->N;
   cudaStream_t st = h->stream;
+  h->sims[0].wait_upload();  // the regression simulations are read from the first kernel on
+  if (h->sims[0].upload_stream) CUDA_OK(cudaStreamSynchronize(h->sims[0].upload_stream));
   h->has_results = false;
   h->scalars = lsmc_results{};
   h->scalars.ms_regression_sim = h->sims[0].ms_simulation;
@@ -668,7 +696,6 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     const double *partials;
     int chunks;
   };
-  constexpr int kGroupTiles = 32;
   auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this, bool fold_done) {
     const PeriodTables &pt = h->tables.periods[p];
     if (has_basis(p - 1)) CUDA_OK(cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0));
@@ -731,13 +758,6 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     if (!terminal && time_steps) CUDA_OK(cudaEventRecord(step_events[2 * p], st));
     StepSums out{h->partials.ptr, (int)tiles};
     if (sweep && h->use_mma && a.ring_rows > 0) {
-      static const bool group_reduce = [] { const char *e = std::getenv("LSMC_GROUP_REDUCE"); return !(e && e[0] == '0'); }();  // test hook
-      if (group_reduce && tiles > 2 * kGroupTiles) {
-        a.group_partials = h->group_partials.ptr;
-        a.group_counters = h->group_counters.ptr;
-        a.group_tiles = kGroupTiles;
-        out = StepSums{h->group_partials.ptr, (int)((tiles + kGroupTiles - 1) / kGroupTiles)};
-      }
       launch_backward_sweep_mma(a, gsplit, tiles, st);
     } else if (sweep) {
       launch_backward_sweep(a, gsplit, tiles, st);
@@ -837,7 +857,11 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     cudaStreamSynchronize(st);
     for (int p = P / 2 + 2; p >= P / 2; --p) {
       float m[5];
-      for (int i = 0; i < 5; ++i) cudaEventElapsedTime(&m[i], tr[5 * (size_t)(P / 2 + 2)], tr[5 * (size_t)p + i]);
+      for (int i = 0; i < 5; ++i)
+        if (cudaEventElapsedTime(&m[i], tr[5 * (size_t)(P / 2 + 2)], tr[5 * (size_t)p + i]) != cudaSuccess) {
+          m[i] = 0.f;  // a mark this code path never recorded (reduction and fold share one launch)
+          cudaGetLastError();
+        }
       std::fprintf(stderr, "[lsmc] step %d: start %.1f us | reduce done %.1f | fold done %.1f | sweep may start %.1f | sweep done %.1f\n", p,
                    1e3 * m[0], 1e3 * m[1], 1e3 * m[2], 1e3 * m[3], 1e3 * m[4]);
     }
@@ -885,20 +909,54 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.step_sums = h->step_sums.ptr;
   fa.sums_width = sums_width;
   fa.tiles_per_cta = (int)((fwd_tiles + fwd_ctas - 1) / fwd_ctas);
-  fa.p_inventory = h->panels[0].ptr;
-  fa.p_volume = h->panels[1].ptr;
-  fa.p_consumed = h->panels[2].ptr;
-  fa.p_loss = h->panels[3].ptr;
-  fa.p_net_volume = h->panels[4].ptr;
-  fa.p_pv = h->panels[5].ptr;
-  fa.p_decision = h->panels[6].ptr;
   fa.error_flag = h->error_flag.ptr;
   fa.snapped = reinterpret_cast<unsigned long long *>(h->error_flag.ptr + 2);
-  launch_forward(fa, fwd_ctas, st);
-  launched("forward_kernel", -1);
-  launches++;
-  // the forward pass is queued behind the last windows: report those while it runs
-  while (windows_reported < windows_enqueued) report_window(windows_reported++);
+  // the valuation simulations may still be on their way (lsmc_set_sims_async): the forward pass is their first reader
+  h->sims[1].wait_upload();
+  if (h->sims[1].upload_stream) CUDA_OK(cudaStreamSynchronize(h->sims[1].upload_stream));
+  double **panel_arg[7] = {&fa.p_inventory, &fa.p_volume, &fa.p_consumed, &fa.p_loss, &fa.p_net_volume, &fa.p_pv, &fa.p_decision};
+  if (!h->stream_panels) {
+    for (int i = 0; i < 7; ++i) *panel_arg[i] = h->panels[i].ptr;
+    fa.p_begin = 0;
+    fa.p_end = P;
+    fa.panel_row0 = 0;
+    launch_forward(fa, fwd_ctas, st);
+    launched("forward_kernel", -1);
+    launches++;
+    // the forward pass is queued behind the last windows: report those while it runs
+    while (windows_reported < windows_enqueued) report_window(windows_reported++);
+  } else {
+    // Streamed panels: blocks of `stream_block` periods alternate between the two halves of every panel ring;
+    // while block b is simulated the host drains block b-1 through the pinned staging buffers into the caller's arrays.
+    for (int i = 0; i < 7; ++i)
+      if (h->panels[i].ptr && !h->sinks[i])
+        throw Error(LSMC_ERR_INVALID_OPERATION, "LSMC_STREAM_PANELS: lsmc_set_panel_sink has not been called for every requested panel.");
+    const int B = h->stream_block, num_blocks = (P + B - 1) / B;
+    auto drain = [&](int b) {  // copies block b's rows of every panel to its sink; blocks the host until done
+      const int first = b * B, rows = std::min(B, P - first);
+      CUDA_OK(cudaStreamWaitEvent(h->copy_stream, h->ev_block[b & 1], 0));
+      for (int i = 0; i < 7; ++i)
+        if (h->panels[i].ptr)
+          h->sink_stager.to_host(h->sinks[i] + (size_t)first * N, h->panels[i].ptr + (size_t)(b & 1) * B * N, (size_t)rows * N * sizeof(double),
+                                 h->copy_stream);
+      CUDA_OK(cudaEventRecord(h->ev_copied[b & 1], h->copy_stream));
+    };
+    for (int b = 0; b < num_blocks; ++b) {
+      if (b >= 2) CUDA_OK(cudaStreamWaitEvent(st, h->ev_copied[b & 1], 0));  // the half this block writes has been drained
+      for (int i = 0; i < 7; ++i) *panel_arg[i] = h->panels[i].ptr ? h->panels[i].ptr + (size_t)(b & 1) * B * N : nullptr;
+      fa.p_begin = b * B;
+      fa.p_end = std::min(P, (b + 1) * B);
+      fa.panel_row0 = fa.p_begin;
+      launch_forward(fa, fwd_ctas, st);
+      launched("forward_kernel", fa.p_begin);
+      launches++;
+      CUDA_OK(cudaEventRecord(h->ev_block[b & 1], st));
+      if (b == 0)
+        while (windows_reported < windows_enqueued) report_window(windows_reported++);
+      if (b >= 1) drain(b - 1);
+    }
+    drain(num_blocks - 1);
+  }
   dbg("forward_kernel", -1);
   launch_reduce_step_sums(h->step_sums.ptr, P, fwd_ctas, sums_width, h->step_totals.ptr, st);
   launches++;
@@ -966,6 +1024,13 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     check_cancel();
   }
 
+  if (h->stream_panels) {  // row P of the streamed [P+1][N] panels: zero, except the inventory the paths end with (LSV.cs:627-629)
+    for (int i = 0; i < 6; ++i)
+      if (h->sinks[i] && h->panels[i].ptr) std::fill(h->sinks[i] + (size_t)P * N, h->sinks[i] + (size_t)(P + 1) * N, 0.0);
+    if (h->sinks[0] && h->panels[0].ptr)
+      CUDA_OK(cudaMemcpy(h->sinks[0] + (size_t)P * N, h->final_inv.ptr, N * sizeof(double), cudaMemcpyDeviceToHost));
+  }
+
   // ---- terminal PV, NPV and standard error (LSV.cs:595-618)
   double end_period_pv = 0.0;
   const bool need_pv_host = !h->model->must_be_empty_at_end();
@@ -999,7 +1064,12 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       if (!last_row.empty()) last_row[n] = add;
     }
     end_period_pv = global_total / total_n;
-    if (!last_row.empty()) CUDA_OK(cudaMemcpy(h->panels[5].ptr + (size_t)P * N, last_row.data(), N * sizeof(double), cudaMemcpyHostToDevice));
+    if (!last_row.empty()) {
+      if (h->stream_panels)
+        std::copy(last_row.begin(), last_row.end(), h->sinks[5] + (size_t)P * N);
+      else
+        CUDA_OK(cudaMemcpy(h->panels[5].ptr + (size_t)P * N, last_row.data(), N * sizeof(double), cudaMemcpyHostToDevice));
+    }
     CUDA_OK(cudaMemcpy(h->pv.ptr, pv.data(), N * sizeof(double), cudaMemcpyHostToDevice));
   }
   {
@@ -1016,6 +1086,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   h->comm.all_reduce_host(&final_inv_sum, 1, st);
 
   h->scalars.snapped_inventories = snapped;
+  h->scalars.ms_upload = h->sims[0].ms_upload + h->sims[1].ms_upload;
   h->scalars.npv = npv;
   h->scalars.std_error = std::sqrt(variance) / std::sqrt(total_n);
   h->scalars.backward_npv = back_sum / total_n;
@@ -1105,12 +1176,6 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
                                       (size_t)((h->Gmax + 7) / 8) * mma_block_record_bytes(h->K)) / sizeof(double));
     h->fold_counter.allocate(1);
     CUDA_OK(cudaMemset(h->fold_counter.ptr, 0, sizeof(unsigned int)));
-    {
-      const size_t groups = (size_t)(num_tiles + 31) / 32;
-      h->group_partials.allocate(groups * h->Gmax * h->acc_k);
-      h->group_counters.allocate(groups * ((h->Gmax + 7) / 8));
-      CUDA_OK(cudaMemset(h->group_counters.ptr, 0, h->group_counters.count * sizeof(unsigned int)));
-    }
     h->qbuf[0].allocate((size_t)h->K * h->pitch);
     h->qbuf[1].allocate((size_t)h->K * h->pitch);
     h->qbuf[2].allocate((size_t)h->K * h->pitch);
@@ -1120,12 +1185,43 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
     h->block_sums.allocate(512);
     const uint32_t panel_flags[6] = {LSMC_RETURN_INVENTORY, LSMC_RETURN_INJECT_WITHDRAW_VOLUME, LSMC_RETURN_CMDTY_CONSUMED,
                                      LSMC_RETURN_INVENTORY_LOSS, LSMC_RETURN_NET_VOLUME, LSMC_RETURN_PV};
-    for (int i = 0; i < 6; ++i)
-      if (h->flags & panel_flags[i]) {
-        h->panels[i].allocate((size_t)(h->P + 1) * h->N);
-        CUDA_OK(cudaMemset(h->panels[i].ptr, 0, h->panels[i].count * sizeof(double)));
+    {
+      int num_panels = (h->flags & LSMC_RETURN_DECISION_INDEX) ? 1 : 0;
+      for (int i = 0; i < 6; ++i)
+        if (h->flags & panel_flags[i]) ++num_panels;
+      h->stream_panels = (h->flags & LSMC_STREAM_PANELS) != 0 && num_panels > 0;
+      size_t free_bytes = 0, total_bytes = 0;
+      CUDA_OK(cudaMemGetInfo(&free_bytes, &total_bytes));
+      const size_t sims_bytes = 2 * (size_t)(1 + h->F) * h->sim_rows * h->N * sizeof(double);  // both simulation sets, allocated later
+      size_t rows_per_panel = (size_t)h->P + 1;
+      if (h->stream_panels) {
+        // two ring halves of `stream_block` periods per panel, sized for about 2 GB of device memory in total
+        const size_t budget = (size_t)2 << 30;
+        h->stream_block = (int)std::max<size_t>(1, std::min<size_t>((size_t)h->P, budget / (2 * (size_t)num_panels * h->N * sizeof(double))));
+        if (const char *env = std::getenv("LSMC_STREAM_BLOCK"))  // test hook: periods per streamed block
+          h->stream_block = std::max(1, std::min(h->P, std::atoi(env)));
+        rows_per_panel = 2 * (size_t)h->stream_block;
+        CUDA_OK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+          CUDA_OK(cudaEventCreateWithFlags(&h->ev_block[i], cudaEventDisableTiming));
+          CUDA_OK(cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming));
+        }
       }
-    if (h->flags & LSMC_RETURN_DECISION_INDEX) h->panels[6].allocate((size_t)h->P * h->N);
+      const size_t panel_bytes = (size_t)num_panels * rows_per_panel * h->N * sizeof(double);
+      if (num_panels > 0 && panel_bytes + sims_bytes > free_bytes) {
+        auto gb = [](size_t b) { return std::to_string((b + ((size_t)1 << 29)) >> 30) + " GB"; };
+        throw Error(LSMC_ERR_ARGUMENT, "SimulationDataReturned asks for " + gb(panel_bytes) + " of per-simulation panels on the device on top of " +
+                                           gb(sims_bytes) + " of simulations, with " + gb(free_bytes) + " free: request fewer panels, add "
+                                           "LSMC_STREAM_PANELS (panels are then delivered to host arrays block by block), or shard the paths "
+                                           "over more GPUs.");
+      }
+      for (int i = 0; i < 6; ++i)
+        if (h->flags & panel_flags[i]) {
+          h->panels[i].allocate(rows_per_panel * h->N);
+          CUDA_OK(cudaMemset(h->panels[i].ptr, 0, h->panels[i].count * sizeof(double)));
+        }
+      if (h->flags & LSMC_RETURN_DECISION_INDEX) h->panels[6].allocate((h->stream_panels ? rows_per_panel : (size_t)h->P) * h->N);
+    }
     build_device_tables(h.get());
     *out = h.release();
     return LSMC_OK;
@@ -1134,28 +1230,53 @@ lsmc_status lsmc_create(const lsmc_problem *pb, int device, lsmc_handle **out) {
   }
 }
 
-static lsmc_status set_sims_impl(lsmc_handle *h, int which, const double *spot, const double *const *factors, bool device_ptrs) {
+static lsmc_status set_sims_impl(lsmc_handle *h, int which, const double *spot, const double *const *factors, bool device_ptrs,
+                                 bool async = false) {
   if (!h) return LSMC_ERR_ARGUMENT;
   try {
     if (which != 0 && which != 1) throw Error(LSMC_ERR_ARGUMENT, "which must be 0 (regression) or 1 (valuation)");
     if (!spot || (h->F > 0 && !factors)) throw Error(LSMC_ERR_ARGUMENT, which == 0 ? "regressionSpotSim is null" : "valuationSpotSim is null");
     CUDA_OK(cudaSetDevice(h->device));
     SimSet &s = h->sims[which];
+    s.wait_upload();  // an earlier asynchronous upload into the same buffers
     const size_t count = (size_t)h->sim_rows * h->N;
+    s.ms_upload = 0.0;
     if (device_ptrs) {
       s.spot = spot;
       for (int i = 0; i < h->F; ++i) s.factors[i] = factors[i];
     } else {
+      for (int i = 0; i < h->F; ++i)
+        if (!factors[i]) throw Error(LSMC_ERR_ARGUMENT, "a factor simulation panel is null");
       s.owned_spot.allocate(count);
-      h->stager.to_device(s.owned_spot.ptr, spot, count * sizeof(double), h->stream);
       s.spot = s.owned_spot.ptr;
       for (int i = 0; i < h->F; ++i) {
-        if (!factors[i]) throw Error(LSMC_ERR_ARGUMENT, "a factor simulation panel is null");
         s.owned_factors[i].allocate(count);
-        h->stager.to_device(s.owned_factors[i].ptr, factors[i], count * sizeof(double), h->stream);
         s.factors[i] = s.owned_factors[i].ptr;
       }
-      CUDA_OK(cudaStreamSynchronize(h->stream));
+      const int F = h->F, device = h->device;
+      std::vector<const double *> src(factors, factors + F);
+      if (async) {
+        if (!s.upload_stream) CUDA_OK(cudaStreamCreateWithFlags(&s.upload_stream, cudaStreamNonBlocking));
+        if (!s.upload_stager) s.upload_stager.reset(new PinnedStager);
+        SimSet *sp = &s;
+        s.uploader = std::thread([sp, spot, src, count, F, device] {
+          try {
+            const auto t0 = std::chrono::steady_clock::now();
+            CUDA_OK(cudaSetDevice(device));
+            sp->upload_stager->to_device(sp->owned_spot.ptr, spot, count * sizeof(double), sp->upload_stream);
+            for (int i = 0; i < F; ++i) sp->upload_stager->to_device(sp->owned_factors[i].ptr, src[i], count * sizeof(double), sp->upload_stream);
+            sp->ms_upload = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+          } catch (...) {
+            sp->upload_error = std::current_exception();
+          }
+        });
+      } else {
+        const auto t0 = std::chrono::steady_clock::now();
+        h->stager.to_device(s.owned_spot.ptr, spot, count * sizeof(double), h->stream);
+        for (int i = 0; i < F; ++i) h->stager.to_device(s.owned_factors[i].ptr, src[i], count * sizeof(double), h->stream);
+        CUDA_OK(cudaStreamSynchronize(h->stream));
+        s.ms_upload = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+      }
     }
     s.ms_simulation = 0.0;
     s.ready = true;
@@ -1173,6 +1294,33 @@ lsmc_status lsmc_set_sims_device(lsmc_handle *h, int which, const double *spot, 
   return set_sims_impl(h, which, spot, factors, true);
 }
 
+lsmc_status lsmc_set_sims_async(lsmc_handle *h, int which, const double *spot, const double *const *factors) {
+  return set_sims_impl(h, which, spot, factors, false, true);
+}
+
+lsmc_status lsmc_set_panel_sink(lsmc_handle *h, lsmc_panel which, double *host_destination) {
+  if (!h) return LSMC_ERR_ARGUMENT;
+  try {
+    if (!h->stream_panels) throw Error(LSMC_ERR_INVALID_OPERATION, "lsmc_set_panel_sink needs LSMC_STREAM_PANELS in SimulationDataReturned.");
+    int slot = -1;
+    switch (which) {
+      case LSMC_PANEL_INVENTORY: slot = 0; break;
+      case LSMC_PANEL_INJECT_WITHDRAW_VOLUME: slot = 1; break;
+      case LSMC_PANEL_CMDTY_CONSUMED: slot = 2; break;
+      case LSMC_PANEL_INVENTORY_LOSS: slot = 3; break;
+      case LSMC_PANEL_NET_VOLUME: slot = 4; break;
+      case LSMC_PANEL_PV: slot = 5; break;
+      case LSMC_PANEL_DECISION_INDEX: slot = 6; break;
+      default: throw Error(LSMC_ERR_ARGUMENT, "only the per-simulation result panels can be streamed");
+    }
+    if (!h->panels[slot].ptr) throw Error(LSMC_ERR_INVALID_OPERATION, "This panel was not requested in SimulationDataReturned.");
+    h->sinks[slot] = host_destination;
+    return LSMC_OK;
+  } catch (const std::exception &e) {
+    return (lsmc_status)status_of(h, e);
+  }
+}
+
 lsmc_status lsmc_simulate(lsmc_handle *h, int which, const lsmc_multi_factor_params *params, uint64_t seed, int antithetic,
                           int64_t first_path_id) {
   if (!h) return LSMC_ERR_ARGUMENT;
@@ -1182,6 +1330,8 @@ lsmc_status lsmc_simulate(lsmc_handle *h, int which, const lsmc_multi_factor_par
     if (params->num_factors != h->F) throw Error(LSMC_ERR_ARGUMENT, "model has a different number of factors than the problem");
     CUDA_OK(cudaSetDevice(h->device));
     SimSet &s = h->sims[which];
+    s.wait_upload();
+    s.ms_upload = 0.0;
     const size_t count = (size_t)h->sim_rows * h->N;
     s.owned_spot.allocate(count);
     double *fac[LSMC_MAX_FACTORS] = {};
@@ -1273,6 +1423,9 @@ lsmc_status lsmc_copy_panel(lsmc_handle *h, lsmc_panel which, double *dst) {
     if (!h->has_results) throw Error(LSMC_ERR_INVALID_OPERATION, "lsmc_run has not completed on this handle.");
     CUDA_OK(cudaSetDevice(h->device));
     const size_t N = h->N;
+    if (h->stream_panels && which != LSMC_PANEL_SPOT_REGRESSION && which != LSMC_PANEL_SPOT_VALUATION &&
+        which != LSMC_PANEL_FACTORS_REGRESSION && which != LSMC_PANEL_FACTORS_VALUATION)
+      throw Error(LSMC_ERR_INVALID_OPERATION, "LSMC_STREAM_PANELS: this panel was delivered to its sink during lsmc_run and is not kept on the device.");
     auto copy = [&](const double *src, size_t count) {
       if (!src) throw Error(LSMC_ERR_INVALID_OPERATION, "This panel was not requested in SimulationDataReturned.");
       h->stager.to_host(dst, src, count * sizeof(double), h->stream);
@@ -1320,6 +1473,8 @@ const char *lsmc_last_error(const lsmc_handle *h) { return h ? h->error.c_str() 
 void lsmc_destroy(lsmc_handle *h) {
   if (!h) return;
   cudaSetDevice(h->device);
+  for (auto &s : h->sims)  // an upload still in flight writes into buffers this call is about to free
+    if (s.uploader.joinable()) s.uploader.join();
   if (h->stream) {
     cudaStreamSynchronize(h->stream);
     if (h->aux_stream) cudaStreamSynchronize(h->aux_stream);
@@ -1328,6 +1483,9 @@ void lsmc_destroy(lsmc_handle *h) {
     for (auto &e : h->ev_basis) if (e) cudaEventDestroy(e);
     for (auto &e : h->ev_step) if (e) cudaEventDestroy(e);
     for (auto &e : h->ev_window) if (e) cudaEventDestroy(e);
+    for (auto &e : h->ev_block) if (e) cudaEventDestroy(e);
+    for (auto &e : h->ev_copied) if (e) cudaEventDestroy(e);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     for (auto &e : h->step_events) if (e) cudaEventDestroy(e);
     if (h->ev_prepass) cudaEventDestroy(h->ev_prepass);
   }

@@ -576,11 +576,14 @@ class Handle:
         except Exception:
             pass
 
-    def set_sims(self, which, spot, factors):
+    def set_sims(self, which, spot, factors, wait=True):
+        """wait=False: lsmc_set_sims_async; the returned arrays must be kept alive until lsmc_run has returned."""
         spot = np.ascontiguousarray(spot, dtype=np.float64)
         facs = [np.ascontiguousarray(f, dtype=np.float64) for f in factors]
         ptrs = (C.c_void_p * max(len(facs), 1))(*[f.ctypes.data for f in facs])
-        self.check(self.lib.lsmc_set_sims(self.h, which, spot.ctypes.data, ptrs))
+        fn = self.lib.lsmc_set_sims if wait else self.lib.lsmc_set_sims_async
+        self.check(fn(self.h, which, spot.ctypes.data, ptrs))
+        return spot, facs
 
     def panel(self, which, rows, n, lead=None):
         shape = (rows, n) if lead is None else (lead, rows, n)
@@ -647,12 +650,17 @@ class LsmcStorageValuation:
             h.check(h.lib.lsmc_comm_init(h.h, s.comm_id, s.rank, s.world, s.total_sims))
         return h
 
-    def Calculate(self, lsmcParams, keep_decisions=False, reference_operation_order=False):
+    # per-simulation result panels larger than this are streamed to the host during the run instead of being kept on the device
+    STREAM_PANELS_ABOVE_BYTES = 1 << 30
+
+    def Calculate(self, lsmcParams, keep_decisions=False, reference_operation_order=False, stream_panels=None):
         """LsmcStorageValuation.Calculate (LSV.cs:57-657).
 
-        keep_decisions and reference_operation_order have no reference counterpart: the first keeps the argmax index panel,
-        the second evaluates each decision's cash flow in the reference's own sequence of roundings (LSV.cs:317-336) instead
-        of the default fused form (include/lsmc_b200.h LSMC_REFERENCE_OPERATION_ORDER)."""
+        keep_decisions, reference_operation_order and stream_panels have no reference counterpart: the first keeps the argmax
+        index panel, the second evaluates each decision's cash flow in the reference's own sequence of roundings
+        (LSV.cs:317-336) instead of the default fused form (include/lsmc_b200.h LSMC_REFERENCE_OPERATION_ORDER), the third
+        forces (True) or forbids (False) delivering the requested per-simulation panels block by block while the forward
+        simulation runs (LSMC_STREAM_PANELS; default: when they exceed STREAM_PANELS_ABOVE_BYTES)."""
         p = lsmcParams
         notify = p.OnProgressUpdate
         if p.Inventory < 0:  # LSV.cs:64-65
@@ -688,8 +696,16 @@ class LsmcStorageValuation:
                 if num_sims != shard.total_sims:
                     raise ArgumentException("PathShard.total_sims differs from the number of simulations of the parameters")
                 num_sims, first_path = shard.num_sims, shard.begin
+        S = SimulationDataReturned
+        result_flags = [S.Inventory, S.InjectWithdrawVolume, S.CmdtyConsumed, S.InventoryLoss, S.NetVolume, S.Pv]
+        num_result_panels = sum(1 for f in result_flags if p.SimulationDataReturned & f) + (1 if keep_decisions else 0)
+        if stream_panels is None:
+            rows = p.Storage.EndPeriod.OffsetFrom(max(p.Storage.StartPeriod, p.CurrentPeriod)) + 1
+            stream_panels = num_result_panels * rows * num_sims * 8 > self.STREAM_PANELS_ABOVE_BYTES
+        stream_panels = bool(stream_panels) and num_result_panels > 0
         flat = FlatProblem(p, num_sims, num_factors, extra_flags=(_abi.LSMC_RETURN_DECISION_INDEX if keep_decisions else 0)
-                           | (_abi.LSMC_REFERENCE_OPERATION_ORDER if reference_operation_order else 0))
+                           | (_abi.LSMC_REFERENCE_OPERATION_ORDER if reference_operation_order else 0)
+                           | (_abi.LSMC_STREAM_PANELS if stream_panels else 0))
         if spec[0] == "panels":  # CheckSpotSim (LVP.cs:219-231): host-side, before any device call
             for name, sims in (("regressionSpotSim", reg), ("valuationSpotSim", val)):
                 have = set(sims.SimulatedPeriods)
@@ -699,10 +715,13 @@ class LsmcStorageValuation:
         h = self._handle_for(flat)
         try:
             lib = h.lib
+            keep_alive = []
             if spec[0] == "panels":
+                # the regression set is needed by the first kernel; the valuation set only by the forward simulation, so it is
+                # handed over without waiting and travels while the backward induction runs
                 for sims, which in ((reg, 0), (val, 1)):
                     rows = sims.rows_for(flat.sim_periods)
-                    h.set_sims(which, sims.SpotPriceSims[rows], [f[rows] for f in sims.FactorSims])
+                    keep_alive.append(h.set_sims(which, sims.SpotPriceSims[rows], [f[rows] for f in sims.FactorSims], wait=(which == 0)))
             else:
                 _, model, _, seed, val_seed, antithetic = spec
                 mp, keep = flat.model_arrays(model, p.CurrentPeriod)
@@ -720,14 +739,25 @@ class LsmcStorageValuation:
             cb = _abi.PROGRESS_FN(on_progress)
             if token is not None and token.is_set():
                 cancel.value = 1
+            streamed = {}
+            if stream_panels:
+                P = flat.num_periods
+                for flag, which in zip(result_flags + [None], (_abi.LSMC_PANEL_INVENTORY, _abi.LSMC_PANEL_INJECT_WITHDRAW_VOLUME,
+                                                               _abi.LSMC_PANEL_CMDTY_CONSUMED, _abi.LSMC_PANEL_INVENTORY_LOSS,
+                                                               _abi.LSMC_PANEL_NET_VOLUME, _abi.LSMC_PANEL_PV, _abi.LSMC_PANEL_DECISION_INDEX)):
+                    wanted = keep_decisions if flag is None else bool(p.SimulationDataReturned & flag)
+                    if wanted:
+                        streamed[which] = np.empty((P if flag is None else P + 1, num_sims), dtype=np.float64)
+                        h.check(lib.lsmc_set_panel_sink(h.h, which, streamed[which].ctypes.data))
             h.check(lib.lsmc_run(h.h, C.cast(cb, C.c_void_p), None, C.addressof(cancel)))
-            return self._collect(h, flat, p, num_sims, num_factors, keep_decisions)
+            del keep_alive
+            return self._collect(h, flat, p, num_sims, num_factors, keep_decisions, streamed)
         finally:
             if not self._reuse:
                 h.close()
 
     @staticmethod
-    def _collect(h, flat, p, num_sims, num_factors, keep_decisions):
+    def _collect(h, flat, p, num_sims, num_factors, keep_decisions, streamed=None):
         P = flat.num_periods
         periods = flat.periods
         deltas = np.zeros(P + 1)
@@ -753,23 +783,28 @@ class LsmcStorageValuation:
         out.KernelLaunches = r.kernel_launches
         out.Timings["backward_kernel"] = r.ms_backward_kernel
         out.Timings["device"] = r.ms_device
+        out.Timings["upload"] = r.ms_upload
         out.BackwardKernelLaunches = r.backward_kernel_launches
         out.SnappedInventories = r.snapped_inventories
         flags = p.SimulationDataReturned
         S = SimulationDataReturned
         rows = len(flat.sim_periods)
+        streamed = streamed or {}
+
+        def result_panel(which, nrows):  # streamed panels were delivered into their sink arrays during the run
+            return streamed[which] if which in streamed else h.panel(which, nrows, num_sims)
         if flags & S.Inventory:
-            out.InventoryBySim = h.panel(_abi.LSMC_PANEL_INVENTORY, P + 1, num_sims)
+            out.InventoryBySim = result_panel(_abi.LSMC_PANEL_INVENTORY, P + 1)
         if flags & S.InjectWithdrawVolume:
-            out.InjectWithdrawVolumeBySim = h.panel(_abi.LSMC_PANEL_INJECT_WITHDRAW_VOLUME, P + 1, num_sims)
+            out.InjectWithdrawVolumeBySim = result_panel(_abi.LSMC_PANEL_INJECT_WITHDRAW_VOLUME, P + 1)
         if flags & S.CmdtyConsumed:
-            out.CmdtyConsumedBySim = h.panel(_abi.LSMC_PANEL_CMDTY_CONSUMED, P + 1, num_sims)
+            out.CmdtyConsumedBySim = result_panel(_abi.LSMC_PANEL_CMDTY_CONSUMED, P + 1)
         if flags & S.InventoryLoss:
-            out.InventoryLossBySim = h.panel(_abi.LSMC_PANEL_INVENTORY_LOSS, P + 1, num_sims)
+            out.InventoryLossBySim = result_panel(_abi.LSMC_PANEL_INVENTORY_LOSS, P + 1)
         if flags & S.NetVolume:
-            out.NetVolumeBySim = h.panel(_abi.LSMC_PANEL_NET_VOLUME, P + 1, num_sims)
+            out.NetVolumeBySim = result_panel(_abi.LSMC_PANEL_NET_VOLUME, P + 1)
         if flags & S.Pv:
-            out.PvByPeriodAndSim = h.panel(_abi.LSMC_PANEL_PV, P + 1, num_sims)
+            out.PvByPeriodAndSim = result_panel(_abi.LSMC_PANEL_PV, P + 1)
         if flags & S.SpotPricesForRegression:
             out.RegressionSpotPriceSim = h.panel(_abi.LSMC_PANEL_SPOT_REGRESSION, rows, num_sims)
         if flags & S.SpotPricesForValuation:
@@ -779,7 +814,7 @@ class LsmcStorageValuation:
         if flags & S.FactorsForValuation:
             out.ValuationMarkovFactors = list(h.panel(_abi.LSMC_PANEL_FACTORS_VALUATION, rows, num_sims, num_factors))
         if keep_decisions:
-            out.DecisionIndexBySim = h.panel(_abi.LSMC_PANEL_DECISION_INDEX, P, num_sims)
+            out.DecisionIndexBySim = result_panel(_abi.LSMC_PANEL_DECISION_INDEX, P)
         out.SimulatedPeriods = list(flat.sim_periods)
         return out
 

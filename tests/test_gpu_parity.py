@@ -250,3 +250,22 @@ def test_caller_simulation_panels_larger_than_one_staging_chunk_round_trip():
     assert res.InventoryBySim.shape == (case.flat.num_periods + 1, 400_000)
     assert np.isfinite(res.Npv)
     print(f"400k x 55 panels in and out, valuation included: {dt:.2f} s")
+
+
+@pytest.mark.parametrize("block", ["7", "64"])
+def test_streamed_panels_equal_resident_panels(monkeypatch, block):
+    """LSMC_STREAM_PANELS: the forward simulation run in blocks of periods, every block's panel rows copied to the
+    caller's arrays while the next block is computed, the per-path state carried between the launches — bit for bit what the
+    one-launch forward simulation with device-resident panels returns (all six result panels, the decision indices, and the
+    scalar results).  Seven-period blocks exercise many ring turns and a ragged last block."""
+    monkeypatch.setenv("LSMC_STREAM_BLOCK", block)
+    for case in (cases.three_factor_ratchets(num_sims=1500, num_days=40, seed=51, flags=SimulationDataReturned.All),
+                 cases.simple_one_factor(num_sims=1009, num_days=30, seed=52, flags=SimulationDataReturned.All, terminal=(-999.0, 0.0, 0.0, 1.0))):
+        from storage_b200 import LsmcStorageValuation
+        resident = LsmcStorageValuation().Calculate(case.params, keep_decisions=True, stream_panels=False)
+        streamed = LsmcStorageValuation().Calculate(case.params, keep_decisions=True, stream_panels=True)
+        assert streamed.Npv == resident.Npv and streamed.ValuationSimStandardError == resident.ValuationSimStandardError
+        for name in ("InventoryBySim", "InjectWithdrawVolumeBySim", "CmdtyConsumedBySim", "InventoryLossBySim", "NetVolumeBySim",
+                     "PvByPeriodAndSim", "DecisionIndexBySim", "PvBySim"):
+            np.testing.assert_array_equal(getattr(streamed, name), getattr(resident, name), err_msg=name)
+        assert list(streamed.Deltas.values()) == list(resident.Deltas.values())
