@@ -800,11 +800,12 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
       // inv + v - loss after a constrained decision) is snapped onto the limit; the reference would throw (CS.cs:88-94).
       if (inventory < pp.min_inventory && pp.min_inventory - inventory <= a.tolerance) inventory = pp.min_inventory, snapped += valid;
       if (inventory > pp.max_inventory && inventory - pp.max_inventory <= a.tolerance) inventory = pp.max_inventory, snapped += valid;
-      DevRange range = storage_range_dev(a, pp, inventory, &err);
+      int perr = 0;  // this path's own status: threads beyond the last path run on placeholder state and must not report
+      DevRange range = storage_range_dev(a, pp, inventory, &perr);
       const double loss = pp.loss * inventory;
       double decisions[LSMC_MAX_DECISIONS];
       const int D = decision_set_dev(range, inventory, loss, pp.next_space_lo, pp.next_space_hi, a.tolerance, a.extra_decisions,
-                                     decisions, &err);
+                                     decisions, &perr);
       const double inv_cost_npv = (inventory * pp.inv_cost) * pp.inv_cost_df;
       double best = 0.0, best_consumed = 0.0, best_immediate = 0.0, best_volume = 0.0;
       int best_d = 0;
@@ -817,7 +818,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
         const double cost_npv = volume > 0.0 ? (pp.inj_cost * volume) * pp.inj_df : (pp.wd_cost * fabs(-volume)) * pp.wd_df;
         const double immediate = ((inject_withdraw_npv - cost_npv) + consumed_npv) - inv_cost_npv;  // LSV.cs:473
         int lo, hi;
-        bracket_dev(s_grid, Gn, after, a.tolerance, a.inv_grid_spacing, &lo, &hi, &err);
+        bracket_dev(s_grid, Gn, after, a.tolerance, a.inv_grid_spacing, &lo, &hi, &perr);
         const double *gl = s_gamma + (size_t)lo * K;
         double c_lo = q[0] * gl[0];
 #pragma unroll
@@ -845,6 +846,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
         }
       }
       const double next_inventory = inventory + best_volume - loss;  // LSV.cs:485
+      if (valid && perr) err = perr;
 
       if (valid) {
         const size_t off = (size_t)(p - a.panel_row0) * a.N + n;

@@ -305,8 +305,13 @@ class SpotSimResultsFromPanels:
         return len(self.FactorSims)
 
     def rows_for(self, periods):
+        """Rows of the panels that hold `periods`: a slice when they are consecutive (the usual case: no copy of the panels is
+        made on the way to the device), else an index list."""
         index = {p: i for i, p in enumerate(self.SimulatedPeriods)}
-        return [index[p] for p in periods]
+        rows = [index[p] for p in periods]
+        if rows and rows == list(range(rows[0], rows[0] + len(rows))):
+            return slice(rows[0], rows[0] + len(rows))
+        return rows
 
 
 # ----------------------------------------------------------------------------------------------------------------
