@@ -64,14 +64,34 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
   const int K = a.K;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r = lane >> 2, c = lane & 3;
-  const int64_t tile = blockIdx.y;
 
+  // Work split.  The step is num_tiles x total_blocks units (a block of 8 grid points of one 128-path tile), numbered tile-major.
+  // Every CTA takes an equal contiguous share of them, so the whole grid is ONE wave of resident CTAs that all finish together
+  // whatever the path count (with a CTA per tile, 977 tiles on 444 slots ran as 2.2 waves and paid for 3).  A share is walked as
+  // segments: the part of it that lies in one tile.  Per segment the per-path operands are loaded and the row ring is started
+  // afresh, then its blocks are swept upwards.
   const int total_blocks = (a.G + kMmaBlockG - 1) / kMmaBlockG;
-  const int bbeg = blockIdx.x * a.subtiles_per_cta;
-  const int nblocks = min(bbeg + a.subtiles_per_cta, total_blocks) - bbeg;
-  if (nblocks <= 0) return;
+  const int64_t total_units = a.num_tiles * total_blocks;
+  const int64_t unit_end = total_units * (blockIdx.x + 1) / gridDim.x;
+  for (int64_t unit = total_units * blockIdx.x / gridDim.x, segment = 0; unit < unit_end; ++segment) {
+  const int64_t tile = unit / total_blocks;
+  const int bbeg = (int)(unit - tile * total_blocks);
+  const int nblocks = (int)min((int64_t)(total_blocks - bbeg), unit_end - unit);
+  unit += nblocks;
   const int gbeg = bbeg * kMmaBlockG;
-  const int glimit = min(a.G, (bbeg + nblocks) * kMmaBlockG) - gbeg;  // grid points of this CTA, addressed 0..glimit-1 below
+  const int glimit = min(a.G, (bbeg + nblocks) * kMmaBlockG) - gbeg;  // grid points of this segment, addressed 0..glimit-1 below
+  if (segment > 0) {  // every warp is done with the previous segment's ring, records and barriers
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < kMmaGens; ++i) {
+        mbar_inval(&s_mbar[i]);
+        mbar_inval(&s_eval[i]);
+      }
+      mbar_inval(&s_gemm[0]);
+      mbar_inval(&s_gemm[1]);
+    }
+    __syncthreads();
+  }
 
   const Rec *recs = reinterpret_cast<const Rec *>(a.point_tables) + bbeg;
   const uint32_t pitch_bytes = (uint32_t)a.pitch * 8u;
@@ -184,7 +204,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
         double sum = src[0];
 #pragma unroll
         for (int w = 1; w < kMmaWarps; ++w) sum += src[(size_t)w * ACC * kMmaBlockG];
-        a.partials[((size_t)(gbeg + g) * gridDim.y + tile) * ACC + k] = sum;
+        a.partials[((size_t)(gbeg + g) * a.num_tiles + tile) * ACC + k] = sum;
       }
     }
   };
@@ -272,6 +292,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     mbar_wait(&s_gemm[bl & 1], (bl >> 1) & 1);
     combine(bl);
   }
+  }  // segments
 }
 
 template <int KSTEPS, int MB>
@@ -284,15 +305,17 @@ void launch_mma(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t 
 
 size_t mma_block_record_bytes(int K) { return mma_record_bytes(mma_ksteps(K)); }
 
+int backward_sweep_mma_ctas_per_sm() { return LSMC_MMA_MIN_CTAS; }
+
 size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta) {
   const int acc = K <= 8 ? 8 : 16;
   return (size_t)ring_rows * kMmaRowPitchBytes + kMmaGens * mma_block_record_bytes(K) + sizeof(double) * 2 * kMmaWarps * acc * kMmaBlockG +
          (size_t)blocks_per_cta * sizeof(SweepBlock);
 }
 
-void launch_backward_sweep_mma(const BackwardStepArgs &a, int gsplit, int64_t num_tiles, cudaStream_t stream) {
-  const dim3 grid(gsplit, (unsigned)num_tiles);
-  const size_t smem = backward_sweep_mma_smem_bytes(a.K, a.ring_rows, a.subtiles_per_cta);
+void launch_backward_sweep_mma(const BackwardStepArgs &a, int num_ctas, cudaStream_t stream) {
+  const dim3 grid((unsigned)num_ctas);
+  const size_t smem = backward_sweep_mma_smem_bytes(a.K, a.ring_rows, (a.G + kMmaBlockG - 1) / kMmaBlockG);
   const int ks = mma_ksteps(a.K);
   const bool wide = a.K > 8;
   static_assert(sizeof(MmaBlockRecord<2>) == 3 * 2 * 32 * 8 + 3 * 8 * sizeof(MmaScalars) + 3 * 8 * 8, "record layout is what mma_record_bytes() says");

@@ -758,7 +758,13 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     if (!terminal && time_steps) CUDA_OK(cudaEventRecord(step_events[2 * p], st));
     StepSums out{h->partials.ptr, (int)tiles};
     if (sweep && h->use_mma && a.ring_rows > 0) {
-      launch_backward_sweep_mma(a, gsplit, tiles, st);
+      // one wave: every resident CTA slot gets an equal share of the (tile, block) units, but no less than four blocks, below
+      // which the per-segment start-up (operands, first ring fill) would outweigh the balance
+      a.num_tiles = tiles;
+      const int64_t units = tiles * ((a.G + 7) / 8);
+      int ctas = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count * backward_sweep_mma_ctas_per_sm(), units / 4));
+      if (const char *forced = std::getenv("LSMC_MMA_CTAS")) ctas = (int)std::max<int64_t>(1, std::min<int64_t>(units, std::atoi(forced)));  // test hook
+      launch_backward_sweep_mma(a, ctas, st);
     } else if (sweep) {
       launch_backward_sweep(a, gsplit, tiles, st);
     } else {
@@ -876,7 +882,12 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   const int sums_width = kForwardSums + K;
   const int64_t fwd_tiles = (N + kThreads - 1) / kThreads;
   constexpr int kForwardMaxTiles = 8;  // per-path state of this many tiles fits beside the period tables in shared memory
-  const int fwd_ctas = (int)std::max<int64_t>(std::min<int64_t>(fwd_tiles, (int64_t)sm_count * 8), (fwd_tiles + kForwardMaxTiles - 1) / kForwardMaxTiles);
+  // The kernel walks all periods, so its CTAs should all be resident at once (4 per SM) or form whole waves of that many: with
+  // 1.65 waves the second wave costs as much as the first.  Tiles are dealt round-robin over the CTAs (tile t -> CTA t mod
+  // ctas), which spreads the CTAs that carry one tile more than the others evenly over the SMs.
+  const int64_t fwd_slots = (int64_t)sm_count * 4;
+  const int64_t fwd_waves = (fwd_tiles + fwd_slots * kForwardMaxTiles - 1) / (fwd_slots * kForwardMaxTiles);
+  const int fwd_ctas = (int)std::min<int64_t>(fwd_tiles, fwd_slots * std::max<int64_t>(1, fwd_waves));
   if (h->step_sums.count < (size_t)P * fwd_ctas * sums_width) h->step_sums.allocate((size_t)P * fwd_ctas * sums_width);
   if (h->step_totals.count < (size_t)P * sums_width) h->step_totals.allocate((size_t)P * sums_width);
   ForwardArgs fa{};
