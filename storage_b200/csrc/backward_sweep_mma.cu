@@ -65,33 +65,23 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r = lane >> 2, c = lane & 3;
 
-  // Work split.  The step is num_tiles x total_blocks units (a block of 8 grid points of one 128-path tile), numbered tile-major.
-  // Every CTA takes an equal contiguous share of them, so the whole grid is ONE wave of resident CTAs that all finish together
-  // whatever the path count (with a CTA per tile, 977 tiles on 444 slots ran as 2.2 waves and paid for 3).  A share is walked as
-  // segments: the part of it that lies in one tile.  Per segment the per-path operands are loaded and the row ring is started
-  // afresh, then its blocks are swept upwards.
+  // Work split.  The first a.whole_tiles CTAs take one whole 128-path tile each (all blocks of 8 grid points); the hardware
+  // hands them to SM slots as slots free up, which balances the SMs dynamically.  The remaining tiles — the last, partial
+  // wave — are cut into a.tail_split pieces each, so that the grid ends on many short CTAs instead of a few long ones (977
+  // tiles on 444 slots ran as 2.2 waves and paid for 3).
   const int total_blocks = (a.G + kMmaBlockG - 1) / kMmaBlockG;
-  const int64_t total_units = a.num_tiles * total_blocks;
-  const int64_t unit_end = total_units * (blockIdx.x + 1) / gridDim.x;
-  for (int64_t unit = total_units * blockIdx.x / gridDim.x, segment = 0; unit < unit_end; ++segment) {
-  const int64_t tile = unit / total_blocks;
-  const int bbeg = (int)(unit - tile * total_blocks);
-  const int nblocks = (int)min((int64_t)(total_blocks - bbeg), unit_end - unit);
-  unit += nblocks;
-  const int gbeg = bbeg * kMmaBlockG;
-  const int glimit = min(a.G, (bbeg + nblocks) * kMmaBlockG) - gbeg;  // grid points of this segment, addressed 0..glimit-1 below
-  if (segment > 0) {  // every warp is done with the previous segment's ring, records and barriers
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      for (int i = 0; i < kMmaGens; ++i) {
-        mbar_inval(&s_mbar[i]);
-        mbar_inval(&s_eval[i]);
-      }
-      mbar_inval(&s_gemm[0]);
-      mbar_inval(&s_gemm[1]);
-    }
-    __syncthreads();
+  int64_t tile = blockIdx.x;
+  int bbeg = 0, nblocks = total_blocks;
+  if (tile >= a.whole_tiles) {
+    const int64_t i = tile - a.whole_tiles;
+    const int piece = (int)(i % a.tail_split);
+    tile = a.whole_tiles + i / a.tail_split;
+    bbeg = total_blocks * piece / a.tail_split;
+    nblocks = total_blocks * (piece + 1) / a.tail_split - bbeg;
   }
+  if (nblocks <= 0) return;
+  const int gbeg = bbeg * kMmaBlockG;
+  const int glimit = min(a.G, (bbeg + nblocks) * kMmaBlockG) - gbeg;  // grid points of this CTA, addressed 0..glimit-1 below
 
   const Rec *recs = reinterpret_cast<const Rec *>(a.point_tables) + bbeg;
   const uint32_t pitch_bytes = (uint32_t)a.pitch * 8u;
@@ -292,7 +282,6 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     mbar_wait(&s_gemm[bl & 1], (bl >> 1) & 1);
     combine(bl);
   }
-  }  // segments
 }
 
 template <int KSTEPS, int MB>
@@ -313,8 +302,8 @@ size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta) {
          (size_t)blocks_per_cta * sizeof(SweepBlock);
 }
 
-void launch_backward_sweep_mma(const BackwardStepArgs &a, int num_ctas, cudaStream_t stream) {
-  const dim3 grid((unsigned)num_ctas);
+void launch_backward_sweep_mma(const BackwardStepArgs &a, cudaStream_t stream) {
+  const dim3 grid((unsigned)(a.whole_tiles + (a.num_tiles - a.whole_tiles) * a.tail_split));
   const size_t smem = backward_sweep_mma_smem_bytes(a.K, a.ring_rows, (a.G + kMmaBlockG - 1) / kMmaBlockG);
   const int ks = mma_ksteps(a.K);
   const bool wide = a.K > 8;

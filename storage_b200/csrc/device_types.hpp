@@ -54,7 +54,9 @@ struct BackwardStepArgs {
   const double *q_prev; // [K][pitch] basis rows of period-1 for the regression sums (NULL with accumulate: mean mode)
   int accumulate;       // 0: no further regression (period 0)
   double *partials;     // [G][num_tiles][acc] per-tile sums of q_prev[k] * v_this[g] (num_tiles = gridDim.y)
-  int64_t num_tiles;    // FP64-mma sweep kernel: 128-path tiles of the step (its CTAs share tiles x blocks equally)
+  // FP64-mma sweep kernel: 128-path tiles of the step; the first whole_tiles get one CTA each, each of the others tail_split CTAs
+  int64_t num_tiles, whole_tiles;
+  int tail_split;
   int subtiles_per_cta; // inventory-grid sub-tiles one CTA sweeps (kMaxGridTile points each; groups of 8 in the ring and sweep kernels)
   const SweepBlock *sweep_blocks;  // row-ring sweep kernel: [blocks of 8 grid points] of this period
   const void *point_tables;  // sweep kernel: [G] per-grid-point records written by fold_tables_kernel

@@ -124,8 +124,8 @@ constexpr int kMmaLookAhead = LSMC_MMA_LOOKAHEAD;  // generations of rows reques
 constexpr int kMmaRowPitchBytes = kSweepTilePaths * 8 + 64;  // consecutive ring rows start in opposite halves of the 32 banks
 size_t mma_block_record_bytes(int K);
 size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta);
-// num_ctas: CTAs that share the step's (tile, block) units equally; a.num_tiles must be set
-void launch_backward_sweep_mma(const BackwardStepArgs &a, int num_ctas, cudaStream_t stream);
+// a.num_tiles, a.whole_tiles and a.tail_split describe the grid (device_types.hpp)
+void launch_backward_sweep_mma(const BackwardStepArgs &a, cudaStream_t stream);
 int backward_sweep_mma_ctas_per_sm();
 void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream);
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream);

@@ -758,13 +758,27 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
     if (!terminal && time_steps) CUDA_OK(cudaEventRecord(step_events[2 * p], st));
     StepSums out{h->partials.ptr, (int)tiles};
     if (sweep && h->use_mma && a.ring_rows > 0) {
-      // one wave: every resident CTA slot gets an equal share of the (tile, block) units, but no less than four blocks, below
-      // which the per-segment start-up (operands, first ring fill) would outweigh the balance
+      // Whole tiles for as many full waves of resident CTA slots as there are; the tiles of the last, partial wave are split
+      // into the number of pieces that minimises (waves of pieces) x (blocks per piece + one block-time of start-up).
+      const int64_t slots = (int64_t)sm_count * backward_sweep_mma_ctas_per_sm();
+      const int blocks = (a.G + 7) / 8;
       a.num_tiles = tiles;
-      const int64_t units = tiles * ((a.G + 7) / 8);
-      int ctas = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count * backward_sweep_mma_ctas_per_sm(), units / 4));
-      if (const char *forced = std::getenv("LSMC_MMA_CTAS")) ctas = (int)std::max<int64_t>(1, std::min<int64_t>(units, std::atoi(forced)));  // test hook
-      launch_backward_sweep_mma(a, ctas, st);
+      a.whole_tiles = tiles / slots * slots;
+      a.tail_split = 1;
+      const int64_t rest = tiles - a.whole_tiles;
+      if (rest > 0) {
+        int64_t best = INT64_MAX;
+        for (int g = 1; g <= std::max(1, std::min(8, blocks / 3)); ++g) {
+          const int64_t cost = ((rest * g + slots - 1) / slots) * ((blocks + g - 1) / g + 1);
+          if (cost < best) best = cost, a.tail_split = g;
+        }
+      }
+      if (const char *forced = std::getenv("LSMC_MMA_TAIL_SPLIT")) {  // test hook: "<whole tiles>,<pieces per remaining tile>"
+        a.whole_tiles = std::max<int64_t>(0, std::min<int64_t>(tiles, std::atoll(forced)));
+        const char *comma = std::strchr(forced, ',');
+        a.tail_split = std::max(1, std::min(blocks, comma ? std::atoi(comma + 1) : 1));
+      }
+      launch_backward_sweep_mma(a, st);
     } else if (sweep) {
       launch_backward_sweep(a, gsplit, tiles, st);
     } else {

@@ -224,8 +224,8 @@ def test_backward_kernel_variants(monkeypatch, variant, gsplit):
     elif variant == "general":
         monkeypatch.setenv("LSMC_SWEEP", "0")
     monkeypatch.setenv("LSMC_GSPLIT", gsplit)
-    if variant == "row_ring":  # the FP64-mma kernel shares (tile, block) units over its CTAs: few long shares / many one-block shares
-        monkeypatch.setenv("LSMC_MMA_CTAS", "5" if gsplit == "1" else "100000")
+    if variant == "row_ring":  # the FP64-mma kernel: whole tiles only / some whole tiles, the others in three pieces
+        monkeypatch.setenv("LSMC_MMA_TAIL_SPLIT", "1000000,1" if gsplit == "1" else "5,3")
     check_case(cases.three_factor_ratchets(num_sims=1500, num_days=40, seed=13))
     check_case(cases.simple_one_factor(num_sims=1009, num_days=30, seed=6))
 
