@@ -367,6 +367,19 @@ class _StorageBuilder:
         self._withdraw_cost = lambda p: (f(p), p.First())
         return self
 
+    def WithPerUnitWithdrawalCostByPeriod(self, costAndCashFlowDate):
+        """Structured form of WithWithdrawalCost(Func) (CmdtyStorage.cs:411) for costs that are proportional to the withdrawn
+        volume: costAndCashFlowDate(period) -> (cost per unit withdrawn in that period, day the cash flow is paid).  This is what
+        the reference's own call-option fixture passes as a Func (tests/Cmdty.Storage.Test/TestHelper.cs:177-195: a strike per
+        withdrawal date, paid on that month's settlement date)."""
+        def cost(p):
+            per_unit, day = costAndCashFlowDate(p)
+            if per_unit < 0:
+                raise ArgumentException("Per unit withdrawal cost must be non-negative.")
+            return float(per_unit), day
+        self._withdraw_cost = cost
+        return self
+
     def WithWithdrawalCost(self, withdrawalCost):
         raise UnsupportedStorageFeature("WithWithdrawalCost(Func) has no device-evaluable form (CmdtyStorage.cs:411); "
                                         "use a per-unit cost.")
