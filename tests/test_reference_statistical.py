@@ -46,7 +46,7 @@ def one_factor_implied_vol(val_date, expiry, spot_vol, mean_reversion):  # TestH
     return spot_vol[expiry] * math.sqrt(variance / t)
 
 
-def test_curves(start, end):  # TestHelper.CreateDailyTestForwardAndSpotVolCurves, TestHelper.cs:87-108
+def make_test_curves(start, end):  # TestHelper.CreateDailyTestForwardAndSpotVolCurves, TestHelper.cs:87-108
     fwd, vol = {}, {}
     for i, d in enumerate(start.EnumerateTo(end)):
         fwd[d] = 53.5 + math.sin(2.0 * math.pi / 365.0 * i) * 24.6
@@ -84,7 +84,7 @@ def three_calls(fwd):  # TestHelper.CreateThreeCallsLikeStorageTestData, TestHel
 
 def three_calls_valuation(num_sims, seed, forward_seed):
     val_date, rate, mean_reversion = Day(2019, 8, 29), 0.09, 16.5
-    fwd, spot_vol = test_curves(val_date, Day(2020, 4, 1))
+    fwd, spot_vol = make_test_curves(val_date, Day(2020, 4, 1))
     storage, inventory, calls = three_calls(fwd)
     b = LsmcValuationParameters.Builder()
     b.CurrentPeriod = val_date
@@ -179,7 +179,7 @@ def test_forced_inject_and_withdraw_npv_almost_equals_trivial_intrinsic_calc(): 
     inject_rate, inject_days, inject_start = 211.5, 20, Day(2019, 12, 20)
     withdraw_rate, withdraw_days, withdraw_start = 187.54, 15, Day(2020, 2, 5)
     inject_cost, inject_consumed, withdraw_cost, withdraw_consumed = 1.23, 0.01, 0.98, 0.015
-    fwd, spot_vol = test_curves(val_date, end)
+    fwd, spot_vol = make_test_curves(val_date, end)
 
     def flat(rate_):
         return [(0.0, (rate_, rate_)), (10_000.0, (rate_, rate_))]
