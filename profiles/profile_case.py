@@ -16,7 +16,9 @@ ap.add_argument("--grid", type=int, default=200)
 ap.add_argument("--runs", type=int, default=1)
 a = ap.parse_args()
 from storage_b200 import LsmcStorageValuation  # noqa: E402
-params, _ = bench.build_params(a.sims, a.days, a.grid)
+cfg = dict(bench.CONFIGS[4], sims=a.sims, days=a.days, grid=a.grid)
+builder, _ = bench.build_params(cfg, a.sims)
+params = builder.Build()
 for i in range(a.runs):
     t0 = time.perf_counter()
     res = LsmcStorageValuation().Calculate(params)
