@@ -691,8 +691,16 @@ __device__ __noinline__ void bisect_dev(const double *grid, int n, double invent
 // interval is computed directly, and if the inventory is further than the tolerance from both of its end points the
 // reference's bisection returns exactly that bracket whatever mid-points it visits.  Grid hits, tolerance cases and
 // out-of-range inventories go through the reference's search.
-__device__ __forceinline__ void bracket_dev(const double *grid, int n, double inventory, double tol, double inv_spacing, int *lower,
-                                            int *upper, int *err) {
+//
+// Within the tolerance of a grid point the reference's answer depends on which mid-points its search visits: for an
+// inventory in (grid[j] - tol, grid[j]] it returns the point itself, (j, j), if mid = j is visited before mid = j - 1, and the
+// bracket (j - 1, j) otherwise; above grid[j] within the tolerance it is always (j, j).  Which of the two mid-points comes
+// first depends only on (n, j), so the host tabulates it per period by running the reference's search on grid[j] itself
+// (first_hit[j] = 1: the point) and the kernel answers those cases without searching as well.  Paths sit on grid points all
+// the time (an empty or full store is one), so the search itself — divergent, ~8 dependent iterations — was 23 % of the forward
+// kernel's samples.  Anything else (outside the grid by more than the tolerance, one-point grids) still runs the search.
+__device__ __forceinline__ void bracket_dev(const double *grid, const uint8_t *__restrict__ first_hit, int n, double inventory, double tol,
+                                            double inv_spacing, int *lower, int *upper, int *err) {
   if (n >= 2) {
     int i = (int)((inventory - grid[0]) * inv_spacing);
     i = max(0, min(i, n - 2));
@@ -700,9 +708,30 @@ __device__ __forceinline__ void bracket_dev(const double *grid, int n, double in
       --i;
     else if (inventory > grid[i + 1] && i < n - 2)
       ++i;
-    if (inventory - grid[i] > tol && grid[i + 1] - inventory > tol) {
+    const double below = inventory - grid[i], above = grid[i + 1] - inventory;
+    if (below > tol && above > tol) {
       *lower = i;
       *upper = i + 1;
+      return;
+    }
+    if (below > 0.0 && below <= tol && above > tol) {  // just above grid[i]
+      *lower = *upper = i;
+      return;
+    }
+    if (below == 0.0 && above > tol) {  // on grid[i]
+      const bool point = i == 0 || first_hit[i];
+      *lower = point ? i : i - 1;
+      *upper = i;
+      return;
+    }
+    if (below > tol && above >= 0.0 && above <= tol) {  // on or just below grid[i + 1]
+      const bool point = first_hit[i + 1];
+      *lower = point ? i + 1 : i;
+      *upper = i + 1;
+      return;
+    }
+    if (below > tol && above < 0.0 && -above <= tol && i == n - 2) {  // just above the last grid point
+      *lower = *upper = n - 1;
       return;
     }
   }
@@ -721,6 +750,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
   double *s_inv = s_stage + kWarps * a.sums_width;                // [tiles_per_cta][kThreads] inventory carried by each path
   double *s_pv = s_inv + (size_t)a.tiles_per_cta * kThreads;       // [tiles_per_cta][kThreads] PV accumulated so far
   int32_t *s_pw = reinterpret_cast<int32_t *>(s_pv + (size_t)a.tiles_per_cta * kThreads);
+  uint8_t *s_first = reinterpret_cast<uint8_t *>(s_pw + K * (1 + F));  // [Gmax] this period's first_hit table (bracket_dev)
   __shared__ DevPeriodParams s_pp;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -749,7 +779,10 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
     const DevPeriodParams pp = s_pp;
     const int Gn = pp.grid_next_count;
     for (int i = threadIdx.x; i < Gn * K; i += blockDim.x) s_gamma[i] = a.gamma[(size_t)p * a.Gmax * K + i];
-    for (int i = threadIdx.x; i < Gn; i += blockDim.x) s_grid[i] = a.grids[(size_t)(p + 1) * a.Gmax + i];
+    for (int i = threadIdx.x; i < Gn; i += blockDim.x) {
+      s_grid[i] = a.grids[(size_t)(p + 1) * a.Gmax + i];
+      s_first[i] = a.bisect_first[(size_t)p * a.Gmax + i];
+    }
     if (!pp.mean_mode)
       for (int i = threadIdx.x; i < K * K; i += blockDim.x)
         s_rinv[i] = dd{a.rinv[((size_t)p * K * K + i) * 2], a.rinv[((size_t)p * K * K + i) * 2 + 1]};
@@ -818,7 +851,7 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
         const double cost_npv = volume > 0.0 ? (pp.inj_cost * volume) * pp.inj_df : (pp.wd_cost * fabs(-volume)) * pp.wd_df;
         const double immediate = ((inject_withdraw_npv - cost_npv) + consumed_npv) - inv_cost_npv;  // LSV.cs:473
         int lo, hi;
-        bracket_dev(s_grid, Gn, after, a.tolerance, a.inv_grid_spacing, &lo, &hi, &perr);
+        bracket_dev(s_grid, s_first, Gn, after, a.tolerance, a.inv_grid_spacing, &lo, &hi, &perr);
         const double *gl = s_gamma + (size_t)lo * K;
         double c_lo = q[0] * gl[0];
 #pragma unroll
@@ -1016,7 +1049,7 @@ size_t backward_smem_bytes(int KP, int D) {
 
 size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width, int tiles_per_cta) {
   return sizeof(double) * ((size_t)Gmax * K + Gmax) + sizeof(dd) * K * K + sizeof(double) * kWarps * sums_width +
-         sizeof(double) * 2 * (size_t)tiles_per_cta * kThreads + sizeof(int32_t) * K * (1 + F) + 16;
+         sizeof(double) * 2 * (size_t)tiles_per_cta * kThreads + sizeof(int32_t) * K * (1 + F) + (size_t)Gmax + 16;
 }
 
 void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream) {

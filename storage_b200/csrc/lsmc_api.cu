@@ -208,6 +208,7 @@ struct lsmc_handle {
   DeviceBuffer<DevDecision> decisions;
   DeviceBuffer<double> point_tables;  // one step's per-grid-point records for the sweep kernel (kernels.hpp FoldArgs)
   DeviceBuffer<int32_t> num_decisions, d_powers, error_flag;
+  DeviceBuffer<uint8_t> bisect_first;  // ForwardArgs::bisect_first
   DeviceBuffer<unsigned int> fold_counter;  // device-wide arrival counter of reduce_fold_kernel (self-resetting)
   std::vector<size_t> window_offset;  // per period: first block in sweep_blocks
   std::vector<int> sweep_ring_rows;   // per period: ring size of the row-ring sweep kernel (0: direct-load sweep kernel)
@@ -461,6 +462,18 @@ void build_device_tables(lsmc_handle *h) {
   std::vector<double> grids((size_t)(P + 1) * Gmax, 0.0);
   for (int p = 0; p <= P; ++p) std::copy(h->tables.periods[p].grid.begin(), h->tables.periods[p].grid.end(), grids.begin() + (size_t)p * Gmax);
   h->grids.upload(grids);
+  {  // which of mid = j and mid = j-1 the reference's bisection meets first, per next-period grid (SH.cs:280-314; bracket_dev)
+    std::vector<uint8_t> first((size_t)P * Gmax, 1);
+    for (int p = 0; p < P; ++p) {
+      const std::vector<double> &g = h->tables.periods[p + 1].grid;
+      for (int j = 1; j < (int)g.size(); ++j) {
+        int lo = j, hi = j;
+        bisect_inventory_space(g.data(), (int)g.size(), g[j], h->tolerance, &lo, &hi);
+        first[(size_t)p * Gmax + j] = lo == hi ? 1 : 0;
+      }
+    }
+    h->bisect_first.upload(first);
+  }
 
   const StorageModel &st = *h->model;
   std::vector<DevPeriodParams> pp(P);
@@ -920,6 +933,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.poly_min = h->poly_min.ptr;
   fa.poly_max = h->poly_max.ptr;
   fa.grids = h->grids.ptr;
+  fa.bisect_first = h->bisect_first.ptr;
   fa.gamma = h->gamma.ptr;
   fa.rinv = h->rinv.ptr;
   fa.powers = h->d_powers.ptr;
