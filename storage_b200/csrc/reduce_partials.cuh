@@ -23,21 +23,21 @@ __device__ __forceinline__ void reduce_partials_body(const ReduceArgs &a, double
   double2 s[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) s[i] = make_double2(0.0, 0.0);
-  int c = lane_c;
-  for (; c + 7 * stride < a.num_chunks; c += 8 * stride) {
+  // batches of eight independent loads per thread; the last, partial batch is predicated instead of walked one load at a
+  // time (a run-time index into s[] would put the accumulators in local memory, and with fewer than 8 x stride chunks — any
+  // rank of a sharded run — that tail is the whole reduction)
+  for (int c = lane_c; c < a.num_chunks; c += 8 * stride) {
     double2 v[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = src[(size_t)(c + i * stride) * pairs];
+    for (int i = 0; i < 8; ++i) {
+      const int ci = c + i * stride;
+      v[i] = ci < a.num_chunks ? src[(size_t)ci * pairs] : make_double2(0.0, 0.0);
+    }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       s[i].x += v[i].x;
       s[i].y += v[i].y;
     }
-  }
-  for (int i = 0; c < a.num_chunks; c += stride, ++i) {
-    const double2 v = src[(size_t)c * pairs];
-    s[i & 7].x += v.x;
-    s[i & 7].y += v.y;
   }
   double2 sum;
   sum.x = ((s[0].x + s[1].x) + (s[2].x + s[3].x)) + ((s[4].x + s[5].x) + (s[6].x + s[7].x));
