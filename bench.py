@@ -429,7 +429,8 @@ def run_gpu(args):
                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": traffic,
                         "traffic_source": traffic_src, "algorithmic_bytes_per_launch": bytes_per_launch,
                         "avg_launch_ms": 1000.0 * avg_kernel_s,
-                        "kernel_share_of_step": (acc["kernel_ms"] / 1000.0 / args.steps) / step_s,
+                        "timed_launches": int(acc["bk_launches"]), "launches_per_step": P,
+                        "kernel_share_of_step": avg_kernel_s * P / step_s,
                         "whole_valuation": {"algorithmic_bytes_per_gpu": whole_bytes, "achieved": whole_bytes / step_s / 1e9,
                                             "frac": whole_bytes / step_s / 1e9 / peak}},
            "e2e": {"value": evals_total / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

@@ -193,8 +193,8 @@ typedef struct lsmc_results {
   double ms_total, ms_regression_sim, ms_valuation_sim, ms_backward, ms_pseudo_inverse, ms_forward;
   int64_t kernel_launches; /* kernels of this library launched by the last lsmc_run */
   /* Device time (CUDA events on the launching stream) of the dominant kernel, the fused backward-induction step, summed
-     over its launches of the last run, and the number of those launches; ms_device is the event time from the first
-     to the last kernel of the run. */
+     over its TIMED launches of the last run, and the number of those launches (every launch up to 64 periods, every 8th
+     beyond; LSMC_STEP_EVENTS=all times all of them); ms_device is the event time from the first to the last kernel of the run. */
   double ms_backward_kernel;
   int64_t backward_kernel_launches;
   double ms_device;

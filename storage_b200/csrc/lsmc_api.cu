@@ -643,7 +643,16 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   const int64_t num_tiles = (N + kTilePaths - 1) / kTilePaths;
   int sm_count = 148;
   CUDA_OK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device));
+  // The dominant kernel is timed with CUDA events around its launch.  An event record between two dependent kernels costs the
+  // GPU front end a little each time, which matters when a step is ~100 us (sharded runs, small configurations): long runs time
+  // every kStepSample-th step (the grid width varies slowly with the period, so the sample is representative), LSMC_STEP_EVENTS=all
+  // times every step, LSMC_NO_STEP_EVENTS none.
   const bool time_steps = std::getenv("LSMC_NO_STEP_EVENTS") == nullptr;
+  const int kStepSample = [&] {
+    const char *e = std::getenv("LSMC_STEP_EVENTS");
+    return (e && e[0] == 'a') || P <= 64 ? 1 : 8;
+  }();
+  auto timed_step = [&](int p) { return time_steps && p % kStepSample == 0; };
   const bool trace = std::getenv("LSMC_TRACE") != nullptr;
   EventList tr(trace ? 5 * (size_t)(P + 1) : 0);
   auto mark = [&](int p, int i) { if (trace) CUDA_OK(cudaEventRecord(tr[5 * (size_t)p + i], st)); };
@@ -768,7 +777,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       a.sweep_blocks = h->sweep_blocks.ptr + h->window_offset[p];
     }
     mark(p, 3);
-    if (!terminal && time_steps) CUDA_OK(cudaEventRecord(step_events[2 * p], st));
+    if (!terminal && timed_step(p)) CUDA_OK(cudaEventRecord(step_events[2 * p], st));
     StepSums out{h->partials.ptr, (int)tiles};
     if (sweep && h->use_mma && a.ring_rows > 0) {
       // Whole tiles for as many full waves of resident CTA slots as there are; the tiles of the last, partial wave are split
@@ -798,7 +807,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       launch_backward_step(a, gsplit, num_tiles, st);
     }
     launched(sweep ? "backward sweep kernel" : "backward_step_kernel", p);
-    if (!terminal && time_steps) CUDA_OK(cudaEventRecord(step_events[2 * p + 1], st));
+    if (!terminal && timed_step(p)) CUDA_OK(cudaEventRecord(step_events[2 * p + 1], st));
     mark(p, 4);
     launches++;
     dbg(sweep ? "backward_sweep_kernel" : "backward_step_kernel", p);
@@ -1138,13 +1147,14 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   h->scalars.ms_device = t_dev.ms();
   {
     double total = 0.0;
-    for (int p = 0; p < P && time_steps; ++p) {
+    int64_t timed = 0;
+    for (int p = 0; p < P; ++p) {
+      if (!timed_step(p)) continue;
       float m = 0.f;
-      cudaEventElapsedTime(&m, step_events[2 * p], step_events[2 * p + 1]);
-      total += m;
+      if (cudaEventElapsedTime(&m, step_events[2 * p], step_events[2 * p + 1]) == cudaSuccess) total += m, ++timed;
     }
     h->scalars.ms_backward_kernel = total;
-    h->scalars.backward_kernel_launches = P;
+    h->scalars.backward_kernel_launches = timed;  // the launches that were timed (every launch, or a regular sample of them)
   }
   h->scalars.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
   h->has_results = true;
