@@ -45,6 +45,12 @@ constexpr int kMmaBlockG = 8;                     // grid points per block = m o
 constexpr int kMmaGroups = 4;                     // 8-path groups per warp
 constexpr int kMmaGens = kMmaLookAhead + 1;       // generations (rows + record of one block) in flight or in use
 constexpr int kMmaRowBytes = kSweepTilePaths * 8;
+#ifndef LSMC_MMA_ACC_LAG
+#define LSMC_MMA_ACC_LAG 2
+#endif
+constexpr int kAccLag = LSMC_MMA_ACC_LAG;         // blocks between a warp writing its regression-sum slice and the slices being combined
+constexpr int kAccBufs = 2 * kAccLag;             // slice buffers: a warp may be kAccLag blocks ahead of the slowest one
+constexpr int kAccBars = kAccLag < 2 ? 2 : kAccLag;  // hand-off barriers: block b + kAccLag must not share one with a block still open
 static_assert(kMmaWarps * kMmaGroups * 8 == kSweepTilePaths, "4 warps x 4 groups x 8 paths = one 128-path tile");
 
 template <int KSTEPS, int MB>
@@ -55,11 +61,11 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
   const int R = a.ring_rows;
   char *s_rows = reinterpret_cast<char *>(smem_raw);                                      // [R][kMmaRowPitchBytes]
   Rec *s_rec = reinterpret_cast<Rec *>(s_rows + (size_t)R * kMmaRowPitchBytes);            // [kMmaGens]
-  double *s_acc = reinterpret_cast<double *>(s_rec + kMmaGens);                            // [2][kMmaWarps][ACC][8]
-  SweepBlock *blk = reinterpret_cast<SweepBlock *>(s_acc + 2 * kMmaWarps * ACC * kMmaBlockG);  // [nblocks]
+  double *s_acc = reinterpret_cast<double *>(s_rec + kMmaGens);                            // [kAccBufs][kMmaWarps][ACC][8]
+  SweepBlock *blk = reinterpret_cast<SweepBlock *>(s_acc + kAccBufs * kMmaWarps * ACC * kMmaBlockG);  // [nblocks]
   __shared__ __align__(8) uint64_t s_mbar[kMmaGens];  // generation j landed (bulk copies, by byte count)
   __shared__ __align__(8) uint64_t s_eval[kMmaGens];  // every warp has evaluated block j: its ring rows and record may be overwritten
-  __shared__ __align__(8) uint64_t s_gemm[2];         // every warp has written its regression-sum slice of block j
+  __shared__ __align__(8) uint64_t s_gemm[kAccBars];  // every warp has written its regression-sum slice of block j
 
   const int K = a.K;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -115,8 +121,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
       mbar_init(&s_mbar[i], 1);
       mbar_init(&s_eval[i], kMmaWarps);
     }
-    mbar_init(&s_gemm[0], kMmaWarps);
-    mbar_init(&s_gemm[1], kMmaWarps);
+    for (int i = 0; i < kAccBars; ++i) mbar_init(&s_gemm[i], kMmaWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -190,7 +195,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
       const int k = item / kMmaBlockG, g8 = item - k * kMmaBlockG;
       const int g = b * kMmaBlockG + g8;
       if (g < glimit) {
-        const double *src = s_acc + (size_t)(b & 1) * kMmaWarps * ACC * kMmaBlockG + item;
+        const double *src = s_acc + (size_t)(b % kAccBufs) * kMmaWarps * ACC * kMmaBlockG + item;
         double sum = src[0];
 #pragma unroll
         for (int w = 1; w < kMmaWarps; ++w) sum += src[(size_t)w * ACC * kMmaBlockG];
@@ -267,20 +272,24 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     vout += (uint64_t)kMmaBlockG * pitch_bytes;
     warp_arrive(&s_eval[b % kMmaGens]);
     if (a.accumulate) {
-      if (b >= 1) {  // slices of block b - 1 are complete once every warp has arrived; then its buffer is free for block b + 1
-        mbar_wait(&s_gemm[(b - 1) & 1], ((b - 1) >> 1) & 1);
-        combine(b - 1);
+      // The slices of a block are combined kAccLag blocks later: by then the other warps have long arrived, so the wait rarely
+      // stalls (with a lag of one block the four warps ran in lock step and these waits were 13 % of the stall samples).  A warp
+      // that has seen s_gemm of block b - kAccLag complete knows every warp has combined block b - 2 kAccLag: that buffer is free.
+      if (b >= kAccLag) {
+        mbar_wait(&s_gemm[(b - kAccLag) % kAccBars], ((b - kAccLag) / kAccBars) & 1);
+        combine(b - kAccLag);
       }
-      double *dst = my_acc + (size_t)(b & 1) * kMmaWarps * ACC * kMmaBlockG;
+      double *dst = my_acc + (size_t)(b % kAccBufs) * kMmaWarps * ACC * kMmaBlockG;
 #pragma unroll
       for (int mb = 0; mb < MB; ++mb) *reinterpret_cast<double2 *>(dst + mb * 8 * kMmaBlockG) = racc[mb];
-      warp_arrive(&s_gemm[b & 1]);
+      warp_arrive(&s_gemm[b % kAccBars]);
     }
   }
   if (a.accumulate) {
-    const int bl = nblocks - 1;
-    mbar_wait(&s_gemm[bl & 1], (bl >> 1) & 1);
-    combine(bl);
+    for (int bb = max(0, nblocks - kAccLag); bb < nblocks; ++bb) {
+      mbar_wait(&s_gemm[bb % kAccBars], (bb / kAccBars) & 1);
+      combine(bb);
+    }
   }
 }
 
@@ -288,6 +297,11 @@ template <int KSTEPS, int MB>
 void launch_mma(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
   ensure_dynamic_smem<backward_sweep_mma_kernel<KSTEPS, MB>>(smem);
   backward_sweep_mma_kernel<KSTEPS, MB><<<grid, kMmaThreads, smem, stream>>>(a);
+  const cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess)
+    throw std::runtime_error("backward_sweep_mma_kernel<" + std::to_string(KSTEPS) + "," + std::to_string(MB) + "> launch failed (" + cudaGetErrorString(e) +
+                             "): grid " + std::to_string(grid.x) + ", dynamic shared memory " + std::to_string(smem) + " B, ring rows " +
+                             std::to_string(a.ring_rows) + ", G " + std::to_string(a.G) + ", tiles " + std::to_string((long long)a.num_tiles));
 }
 
 }  // namespace
@@ -298,7 +312,7 @@ int backward_sweep_mma_ctas_per_sm() { return LSMC_MMA_MIN_CTAS; }
 
 size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta) {
   const int acc = K <= 8 ? 8 : 16;
-  return (size_t)ring_rows * kMmaRowPitchBytes + kMmaGens * mma_block_record_bytes(K) + sizeof(double) * 2 * kMmaWarps * acc * kMmaBlockG +
+  return (size_t)ring_rows * kMmaRowPitchBytes + kMmaGens * mma_block_record_bytes(K) + sizeof(double) * kAccBufs * kMmaWarps * acc * kMmaBlockG +
          (size_t)blocks_per_cta * sizeof(SweepBlock);
 }
 

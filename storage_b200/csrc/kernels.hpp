@@ -83,7 +83,7 @@ __host__ __device__ inline size_t xchg_buffer_bytes(int world, size_t capacity) 
 // launch costs host time in the per-step loop), and reports a refusal instead of letting the launch fail later.
 template <auto Kernel>
 inline void ensure_dynamic_smem(size_t smem) {
-  if (smem <= 48 * 1024) return;
+  if (smem + 4096 <= 48 * 1024) return;  // the default limit counts the kernel's static shared memory too: leave room for it
   constexpr int kDevices = 64;
   static std::atomic<size_t> granted[kDevices] = {};
   int dev = 0;
