@@ -114,6 +114,7 @@ __global__ void fold_tables_kernel(FoldArgs f) {
 // launch that would otherwise queue behind the basis kernel of the second stream.
 template <int KC>
 __global__ void __launch_bounds__(kReduceThreads) reduce_fold_kernel(ReduceArgs r, FoldArgs f, unsigned int *counter) {
+  asm volatile("griddepcontrol.launch_dependents;");  // the sweep kernel behind this one may start its prologue now (it waits for the records)
   reduce_partials_body(r);
   __shared__ bool s_last;
   __threadfence();  // this CTA's gamma row is visible device-wide before it is counted
@@ -157,6 +158,7 @@ __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned l
 
 template <int KC>
 __global__ void __launch_bounds__(kReduceThreads) exchange_fold_kernel(ReduceArgs r, FoldArgs f, XchgArgs x, unsigned int *counter) {
+  asm volatile("griddepcontrol.launch_dependents;");  // as in reduce_fold_kernel
   const int count = r.G * r.K;
   const size_t data_off = xchg_data_offset(x.world);
   const size_t slot = ((size_t)(x.seq & 1) * x.world + x.rank) * x.capacity;  // this rank's slot in every inbox

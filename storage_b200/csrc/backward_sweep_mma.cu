@@ -24,6 +24,9 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
+#include <stdexcept>
+#include <string>
 
 #include "backward_common.cuh"
 #include "device_types.hpp"
@@ -95,7 +98,10 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
   for (int i = threadIdx.x; i < nblocks; i += kMmaThreads) blk[i] = a.sweep_blocks[bbeg + i];
 
   // Generation j = what block j needs that is not resident yet: the rows its window adds to the ring and its record.
-  auto issue_generation = [&](int j) {  // one whole warp: lane 0 posts the byte count, then every lane issues one row
+  auto issue_record = [&](int j) {  // the block's record (written by the kernel that precedes this one in the stream)
+    if (lane == 0) bulk_load(s_rec + j % kMmaGens, recs + j, (uint32_t)sizeof(Rec), &s_mbar[j % kMmaGens]);
+  };
+  auto issue_rows = [&](int j) {  // one whole warp: lane 0 posts the generation's byte count, then every lane issues one row
     uint64_t *bar = &s_mbar[j % kMmaGens];
     int first_row, first_slot, count;
     if (j == 0) {
@@ -104,10 +110,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
       const SweepBlock cur = blk[j - 1], nxt = blk[j];
       first_row = cur.hi + 1, first_slot = cur.hi_slot + 1, count = nxt.hi - cur.hi;
     }
-    if (lane == 0) {
-      mbar_expect_tx(bar, (uint32_t)count * kMmaRowBytes + (uint32_t)sizeof(Rec));
-      bulk_load(s_rec + j % kMmaGens, recs + j, (uint32_t)sizeof(Rec), bar);
-    }
+    if (lane == 0) mbar_expect_tx(bar, (uint32_t)count * kMmaRowBytes + (uint32_t)sizeof(Rec));
     __syncwarp();
 #pragma unroll 1
     for (int i = lane; i < count; i += 32) {
@@ -125,8 +128,15 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (warp == 0)
-    for (int j = 0; j < min(kMmaGens, nblocks); ++j) issue_generation(j);
+  // Programmatic dependent launch: this grid may start while the per-step reduction / exchange + fold kernel before it is
+  // still running (that kernel lets its dependents go at once).  Everything up to here, the first generations' rows (V_{p+1}
+  // is older than that kernel) and the per-path operand loads below overlap its tail — its last CTA folds the records alone
+  // while the rest of the GPU would idle; only the records must wait for it.  Launched without the attribute the wait is a no-op.
+  if (warp == 0) {
+    for (int j = 0; j < min(kMmaGens, nblocks); ++j) issue_rows(j);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    for (int j = 0; j < min(kMmaGens, nblocks); ++j) issue_record(j);
+  }
 
   // ---- per-path operands, loaded once
   // Columns in [N, pitch) are padding of the row buffers: zero in the basis rows and in the terminal values, hence finite in
@@ -210,7 +220,8 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     // instead, with one more block of look-ahead, was measured 5-7 % slower.
     if (b > 0 && b + kMmaLookAhead < nblocks && warp == (b & 3)) {
       mbar_wait(&s_eval[(b - 1) % kMmaGens], ((b - 1) / kMmaGens) & 1);
-      issue_generation(b + kMmaLookAhead);
+      issue_rows(b + kMmaLookAhead);
+      issue_record(b + kMmaLookAhead);
     }
     mbar_wait(&s_mbar[b % kMmaGens], (b / kMmaGens) & 1);  // this block's rows and record have landed
     const Rec *rec = s_rec + b % kMmaGens;
@@ -298,7 +309,18 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
 template <int KSTEPS, int MB>
 void launch_mma(const BackwardStepArgs &a, dim3 grid, size_t smem, cudaStream_t stream) {
   ensure_dynamic_smem<backward_sweep_mma_kernel<KSTEPS, MB>>(smem);
-  backward_sweep_mma_kernel<KSTEPS, MB><<<grid, kMmaThreads, smem, stream>>>(a);
+  static const bool pdl = [] { const char *e = std::getenv("LSMC_PDL"); return !(e && e[0] == '0'); }();  // test hook: 0 = plain launches
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kMmaThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, backward_sweep_mma_kernel<KSTEPS, MB>, a);
   const cudaError_t e = cudaPeekAtLastError();
   if (e != cudaSuccess)
     throw std::runtime_error("backward_sweep_mma_kernel<" + std::to_string(KSTEPS) + "," + std::to_string(MB) + "> launch failed (" + cudaGetErrorString(e) +

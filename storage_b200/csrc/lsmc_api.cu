@@ -720,7 +720,6 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   };
   auto launch_step = [&](int p, bool terminal, const double *v_next, double *v_this, bool fold_done) {
     const PeriodTables &pt = h->tables.periods[p];
-    if (has_basis(p - 1)) CUDA_OK(cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0));
     BackwardStepArgs a{};
     a.N = N;
     a.pitch = h->pitch;
@@ -865,6 +864,12 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
 
   double *v_next = h->v_a.ptr, *v_this = h->v_b.ptr;
   const auto enqueue0 = std::chrono::steady_clock::now();
+  // the basis rows a step needs (period p - 1, for the regression sums) are waited for BEFORE the step's reduction kernel, so that
+  // nothing stands between that kernel and the sweep kernel that may overlap its tail (programmatic dependent launch)
+  auto wait_basis_for_step = [&](int p) {
+    if (has_basis(p - 1)) CUDA_OK(cudaStreamWaitEvent(st, h->ev_basis[(p - 1) % 3], 0));
+  };
+  wait_basis_for_step(P);
   StepSums chunks = launch_step(P, true, nullptr, v_next, false);
   const double back_step = 0.66 / P;  // BackwardPcntTime (LSV.cs:48,164)
   double prog = 0.0;
@@ -884,6 +889,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   };
   for (int p = P - 1; p >= 0; --p) {
     mark(p, 0);
+    wait_basis_for_step(p);
     const bool folded = reduce_gamma(p, (int)h->tables.periods[p + 1].grid.size(), chunks);
     launched("per-step reduction", p);
     chunks = launch_step(p, false, v_next, v_this, folded);
