@@ -789,7 +789,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
       const int64_t rest = tiles - a.whole_tiles;
       if (rest > 0) {
         int64_t best = INT64_MAX;
-        for (int g = 1; g <= std::max(1, std::min(8, blocks / 3)); ++g) {
+        for (int g = 1; g <= std::max(1, std::min(12, blocks / 2)); ++g) {
           const int64_t cost = ((rest * g + slots - 1) / slots) * ((blocks + g - 1) / g + 1);
           if (cost < best) best = cost, a.tail_split = g;
         }
