@@ -96,7 +96,9 @@ struct ForwardArgs {
   const double *ratchet_min_slope, *ratchet_max_slope;  // per ratchet segment: (y[k+1]-y[k]) / (x[k+1]-x[k]) (piecewise-linear kind)
   const double *poly_min, *poly_max;
   const double *grids;             // [P+1][Gmax]
-  const uint8_t *bisect_first;     // [P][Gmax]: for the grid of period p+1, 1 where the reference's BisectInventorySpace meets mid = j
+  int first_pitch;                 // row pitch of bisect_first, a multiple of 16 (forward_first_pitch)
+  int table_buffers;               // shared-memory copies of a period's tables: 2 = the next period's are fetched under this period's arithmetic
+  const uint8_t *bisect_first;     // [P][first_pitch]: for the grid of period p+1, 1 where the reference's BisectInventorySpace meets mid = j
                                    //            before mid = j-1 (kernels.cu bracket_dev)
   const double *gamma;             // [P][Gmax][K]
   const double *rinv;              // [P][K*K*2]

@@ -741,20 +741,27 @@ __device__ __forceinline__ void bracket_dev(const double *grid, const uint8_t *_
   bisect_dev(grid, n, inventory, tol, lower, upper, err);
 }
 
+__device__ __forceinline__ void cp_async8(void *dst_smem, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 template <int KP>
 __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(ForwardArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int K = a.K, F = a.F;
-  // dynamic smem: gamma [Gmax][K] | grid_next [Gmax] | rinv [K*K] dd | powers | warp staging
-  double *s_gamma = reinterpret_cast<double *>(smem_raw);
-  double *s_grid = s_gamma + (size_t)a.Gmax * K;
-  dd *s_rinv = reinterpret_cast<dd *>(s_grid + a.Gmax);
-  double *s_stage = reinterpret_cast<double *>(s_rinv + K * K);  // [kWarps][sums_width]
+  // dynamic smem: a.table_buffers x { DevPeriodParams | gamma [Gmax][K] | grid_next [Gmax] | rinv [K*K] dd | first_hit [first_pitch] }
+  //               | warp staging | per-path state | powers
+  const ForwardTableLayout lay = forward_table_layout(K, a.Gmax, a.first_pitch);
+  unsigned char *s_tables = smem_raw;
+  double *s_stage = reinterpret_cast<double *>(smem_raw + (size_t)a.table_buffers * lay.bytes);  // [kWarps][sums_width]
   double *s_inv = s_stage + kWarps * a.sums_width;                // [tiles_per_cta][kThreads] inventory carried by each path
   double *s_pv = s_inv + (size_t)a.tiles_per_cta * kThreads;       // [tiles_per_cta][kThreads] PV accumulated so far
   int32_t *s_pw = reinterpret_cast<int32_t *>(s_pv + (size_t)a.tiles_per_cta * kThreads);
-  uint8_t *s_first = reinterpret_cast<uint8_t *>(s_pw + K * (1 + F));  // [Gmax] this period's first_hit table (bracket_dev)
-  __shared__ DevPeriodParams s_pp;
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ MonomialProgram s_prog;
@@ -762,9 +769,29 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
   __syncthreads();
   if (threadIdx.x == 0) build_monomial_program(s_prog, s_pw, K, F);
 
+  // The tables of a period (its parameters, the regression coefficients and the grid of the next period, R^-1, the first-visit
+  // table of bracket_dev) are copied into shared memory asynchronously (cp.async), whole rows of the period-major device
+  // arrays whatever the period's own grid size.  With two buffers the copy of period p + 1 is issued at the top of period p
+  // and lands under its arithmetic, so a period costs one CTA barrier for the tables instead of three and no exposed load
+  // latency: that is what a CTA with one or two path tiles (small path counts, many GPUs) spends its time on otherwise.
+  auto stage_tables = [&](int p, int buf) {
+    unsigned char *dst = s_tables + (size_t)buf * lay.bytes;
+    const char *pp_src = reinterpret_cast<const char *>(a.periods + p);
+    for (int i = threadIdx.x; i < (int)(sizeof(DevPeriodParams) / 16); i += blockDim.x) cp_async16(dst + lay.params + 16 * i, pp_src + 16 * i);
+    const double *gamma_src = a.gamma + (size_t)p * a.Gmax * K;
+    for (int i = threadIdx.x; i < a.Gmax * K; i += blockDim.x) cp_async8(dst + lay.gamma + 8 * (size_t)i, gamma_src + i);
+    const double *grid_src = a.grids + (size_t)(p + 1) * a.Gmax;
+    for (int i = threadIdx.x; i < a.Gmax; i += blockDim.x) cp_async8(dst + lay.grid + 8 * (size_t)i, grid_src + i);
+    const double *rinv_src = a.rinv + (size_t)p * K * K * 2;  // (hi, lo) pairs: the layout of dd
+    for (int i = threadIdx.x; i < K * K; i += blockDim.x) cp_async16(dst + lay.rinv + 16 * (size_t)i, rinv_src + 2 * i);
+    const uint8_t *first_src = a.bisect_first + (size_t)p * a.first_pitch;
+    for (int i = threadIdx.x; i < a.first_pitch / 16; i += blockDim.x) cp_async16(dst + lay.first + 16 * (size_t)i, first_src + 16 * i);
+    cp_async_commit();
+  };
+
   // A CTA owns tiles blockIdx.x, blockIdx.x + gridDim.x, ... (at most a.tiles_per_cta of them).  Periods are the outer loop so
-  // that the period's tables (regression coefficients, next grid, R^-1) are staged once per CTA and period; the state a path
-  // carries from one period to the next (inventory, PV so far) waits in shared memory.
+  // that the period's tables are staged once per CTA and period; the state a path carries from one period to the next
+  // (inventory, PV so far) waits in shared memory.
   const int64_t num_tiles = (a.N + kThreads - 1) / kThreads;
   for (int t = 0; t < a.tiles_per_cta; ++t) {
     const int64_t n = (blockIdx.x + (int64_t)t * gridDim.x) * kThreads + threadIdx.x;
@@ -775,21 +802,24 @@ __global__ void __launch_bounds__(kThreads, LSMC_FWD_MIN_CTAS) forward_kernel(Fo
   int err = 0;
   unsigned long long snapped = 0;  // inventories moved onto a limit (lsmc_results.snapped_inventories)
 
+  const bool two = a.table_buffers > 1;
+  if (two && a.p_begin < a.p_end) stage_tables(a.p_begin, 0);
   for (int p = a.p_begin; p < a.p_end; ++p) {
-    __syncthreads();  // previous period's shared tables are no longer in use
-    if (threadIdx.x == 0) s_pp = a.periods[p];
-    __syncthreads();
-    const DevPeriodParams pp = s_pp;
-    const int Gn = pp.grid_next_count;
-    for (int i = threadIdx.x; i < Gn * K; i += blockDim.x) s_gamma[i] = a.gamma[(size_t)p * a.Gmax * K + i];
-    for (int i = threadIdx.x; i < Gn; i += blockDim.x) {
-      s_grid[i] = a.grids[(size_t)(p + 1) * a.Gmax + i];
-      s_first[i] = a.bisect_first[(size_t)p * a.Gmax + i];
+    const int buf = two ? (p - a.p_begin) & 1 : 0;
+    if (!two) {
+      __syncthreads();  // previous period's tables are no longer in use
+      stage_tables(p, 0);
     }
-    if (!pp.mean_mode)
-      for (int i = threadIdx.x; i < K * K; i += blockDim.x)
-        s_rinv[i] = dd{a.rinv[((size_t)p * K * K + i) * 2], a.rinv[((size_t)p * K * K + i) * 2 + 1]};
-    __syncthreads();
+    cp_async_wait_all();
+    __syncthreads();  // this period's tables have landed; nobody reads the other buffer (period p - 1) or s_stage any more
+    if (two && p + 1 < a.p_end) stage_tables(p + 1, buf ^ 1);
+    const unsigned char *tab = s_tables + (size_t)buf * lay.bytes;
+    const DevPeriodParams &pp = *reinterpret_cast<const DevPeriodParams *>(tab + lay.params);
+    const double *s_gamma = reinterpret_cast<const double *>(tab + lay.gamma);
+    const double *s_grid = reinterpret_cast<const double *>(tab + lay.grid);
+    const dd *s_rinv = reinterpret_cast<const dd *>(tab + lay.rinv);
+    const uint8_t *s_first = tab + lay.first;
+    const int Gn = pp.grid_next_count;
 
     double sums[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // this thread's paths, tile after tile
     double qsum[KP];
@@ -1050,9 +1080,9 @@ size_t backward_smem_bytes(int KP, int D) {
                                                 (size_t)kWarps * acc * tg + tg) + sizeof(int32_t) * tg + 16;
 }
 
-size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width, int tiles_per_cta) {
-  return sizeof(double) * ((size_t)Gmax * K + Gmax) + sizeof(dd) * K * K + sizeof(double) * kWarps * sums_width +
-         sizeof(double) * 2 * (size_t)tiles_per_cta * kThreads + sizeof(int32_t) * K * (1 + F) + (size_t)Gmax + 16;
+size_t forward_smem_bytes(int K, int F, int Gmax, int first_pitch, int table_buffers, int sums_width, int tiles_per_cta) {
+  return (size_t)table_buffers * forward_table_layout(K, Gmax, first_pitch).bytes + sizeof(double) * kWarps * sums_width +
+         sizeof(double) * 2 * (size_t)tiles_per_cta * kThreads + sizeof(int32_t) * K * (1 + F) + 16;
 }
 
 void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream) {
@@ -1080,7 +1110,8 @@ void launch_reduce_partials(const ReduceArgs &a, cudaStream_t stream) {
   reduce_partials_kernel<<<a.G, threads, 0, stream>>>(a);
 }
 void launch_forward(const ForwardArgs &a, int num_ctas, cudaStream_t stream) {
-  dispatch(padded_basis(a.K), 3, &a, dim3(num_ctas), dim3(kThreads), forward_smem_bytes(a.K, a.F, a.Gmax, a.sums_width, a.tiles_per_cta), stream);
+  dispatch(padded_basis(a.K), 3, &a, dim3(num_ctas), dim3(kThreads),
+           forward_smem_bytes(a.K, a.F, a.Gmax, a.first_pitch, a.table_buffers, a.sums_width, a.tiles_per_cta), stream);
 }
 void launch_combine_ranks(const double *all, int world, int count, int K, int mean_mode, double total_paths, double *out,
                           cudaStream_t stream) {

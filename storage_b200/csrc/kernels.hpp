@@ -99,7 +99,22 @@ inline void ensure_dynamic_smem(size_t smem) {
 int padded_basis(int K);
 inline int acc_width(int K) { return padded_basis(K) <= 8 ? 8 : 16; }
 size_t backward_smem_bytes(int KP, int D);
-size_t forward_smem_bytes(int K, int F, int Gmax, int sums_width, int tiles_per_cta);
+// One period's tables of the forward kernel in shared memory (byte offsets inside a table buffer, every part 16-byte aligned)
+struct ForwardTableLayout {
+  uint32_t params, gamma, grid, rinv, first, bytes;
+};
+__host__ __device__ inline ForwardTableLayout forward_table_layout(int K, int Gmax, int first_pitch) {
+  ForwardTableLayout l;
+  l.params = 0;
+  l.gamma = (uint32_t)sizeof(DevPeriodParams);
+  l.grid = l.gamma + (((uint32_t)Gmax * K * 8u + 15u) & ~15u);
+  l.rinv = l.grid + (((uint32_t)Gmax * 8u + 15u) & ~15u);
+  l.first = l.rinv + (uint32_t)K * K * 16u;
+  l.bytes = l.first + (uint32_t)first_pitch;
+  return l;
+}
+inline int forward_first_pitch(int Gmax) { return (Gmax + 15) & ~15; }  // row pitch of ForwardArgs::bisect_first: whole 16-byte copies
+size_t forward_smem_bytes(int K, int F, int Gmax, int first_pitch, int table_buffers, int sums_width, int tiles_per_cta);
 
 void launch_gram(const GramArgs &a, int num_chunks, int num_slots, cudaStream_t stream);
 void launch_cholesky(const CholeskyArgs &a, int num_slots, cudaStream_t stream);

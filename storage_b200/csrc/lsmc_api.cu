@@ -463,13 +463,14 @@ void build_device_tables(lsmc_handle *h) {
   for (int p = 0; p <= P; ++p) std::copy(h->tables.periods[p].grid.begin(), h->tables.periods[p].grid.end(), grids.begin() + (size_t)p * Gmax);
   h->grids.upload(grids);
   {  // which of mid = j and mid = j-1 the reference's bisection meets first, per next-period grid (SH.cs:280-314; bracket_dev)
-    std::vector<uint8_t> first((size_t)P * Gmax, 1);
+    const size_t pitch = (size_t)forward_first_pitch(Gmax);
+    std::vector<uint8_t> first((size_t)P * pitch, 1);
     for (int p = 0; p < P; ++p) {
       const std::vector<double> &g = h->tables.periods[p + 1].grid;
       for (int j = 1; j < (int)g.size(); ++j) {
         int lo = j, hi = j;
         bisect_inventory_space(g.data(), (int)g.size(), g[j], h->tolerance, &lo, &hi);
-        first[(size_t)p * Gmax + j] = lo == hi ? 1 : 0;
+        first[(size_t)p * pitch + j] = lo == hi ? 1 : 0;
       }
     }
     h->bisect_first.upload(first);
@@ -949,6 +950,7 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.poly_max = h->poly_max.ptr;
   fa.grids = h->grids.ptr;
   fa.bisect_first = h->bisect_first.ptr;
+  fa.first_pitch = forward_first_pitch(Gmax);
   fa.gamma = h->gamma.ptr;
   fa.rinv = h->rinv.ptr;
   fa.powers = h->d_powers.ptr;
@@ -963,6 +965,11 @@ void run_valuation(lsmc_handle *h, lsmc_progress_fn progress, void *user, const 
   fa.step_sums = h->step_sums.ptr;
   fa.sums_width = sums_width;
   fa.tiles_per_cta = (int)((fwd_tiles + fwd_ctas - 1) / fwd_ctas);
+  // Two table buffers (the next period's tables fetched under this period's arithmetic) when a CTA carries one or two tiles and
+  // has nothing else to hide the fetch behind: cfg 1 forward pass -6 %, cfg 2 -3 %.  With many tiles per CTA the other CTAs of
+  // the SM cover it already and the second buffer only costs (1M paths: +3 %), so one buffer is used there.
+  fa.table_buffers = fa.tiles_per_cta <= 2 && forward_smem_bytes(K, F, Gmax, fa.first_pitch, 2, sums_width, fa.tiles_per_cta) <= 54 * 1024 ? 2 : 1;
+  if (const char *e = std::getenv("LSMC_FWD_TABLE_BUFFERS")) fa.table_buffers = std::atoi(e) >= 2 ? 2 : 1;  // test hook
   fa.error_flag = h->error_flag.ptr;
   fa.snapped = reinterpret_cast<unsigned long long *>(h->error_flag.ptr + 2);
   // the valuation simulations may still be on their way (lsmc_set_sims_async): the forward pass is their first reader

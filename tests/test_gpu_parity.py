@@ -271,3 +271,24 @@ def test_streamed_panels_equal_resident_panels(monkeypatch, block):
                      "PvByPeriodAndSim", "DecisionIndexBySim", "PvBySim"):
             np.testing.assert_array_equal(getattr(streamed, name), getattr(resident, name), err_msg=name)
         assert list(streamed.Deltas.values()) == list(resident.Deltas.values())
+
+
+def test_forward_table_staging_modes_agree(monkeypatch):
+    """The forward kernel stages a period's tables in one shared-memory buffer (many path tiles per CTA) or in two, the next
+    period's tables fetched under the current period's arithmetic (one or two tiles per CTA): same arithmetic, so bit-identical
+    results, resident and with streamed panels (the launch of a period block starts a fresh buffer sequence)."""
+    from storage_b200 import LsmcStorageValuation
+    monkeypatch.setenv("LSMC_STREAM_BLOCK", "7")
+    for case in (cases.three_factor_ratchets(num_sims=1500, num_days=40, seed=61, flags=SimulationDataReturned.All),
+                 cases.simple_one_factor(num_sims=1009, num_days=30, seed=62, flags=SimulationDataReturned.All)):
+        results = {}
+        for buffers in ("1", "2"):
+            monkeypatch.setenv("LSMC_FWD_TABLE_BUFFERS", buffers)
+            results[buffers] = [LsmcStorageValuation().Calculate(case.params, keep_decisions=True, stream_panels=s) for s in (False, True)]
+        one = results["1"][0]
+        for res in (results["1"][1], results["2"][0], results["2"][1]):
+            assert res.Npv == one.Npv and res.ValuationSimStandardError == one.ValuationSimStandardError
+            for name in ("InventoryBySim", "InjectWithdrawVolumeBySim", "PvByPeriodAndSim", "DecisionIndexBySim", "PvBySim"):
+                np.testing.assert_array_equal(getattr(res, name), getattr(one, name), err_msg=name)
+            assert list(res.Deltas.values()) == list(one.Deltas.values())
+        check_case(case)  # and the default mode against the oracle
