@@ -51,6 +51,22 @@ int main(int argc, char **argv) {
       printf("%s depth %d: %.3f ms/launch  %.0f GB/s (read+write)\n", layout ? "tile-major" : "row-major ", depth, ms / reps,
              2.0 * 8 * pitch * G / (ms / reps * 1e-3) / 1e9);
     }
+  // sustained: the row-major walk, depth 4, back to back for about `seconds` (argv[3]) — what the same traffic reaches under
+  // the board's power cap, which a 5 ms burst does not feel
+  const double seconds = argc > 3 ? atof(argv[3]) : 0.0;
+  if (seconds > 0.0) {
+    const int reps = (int)(seconds / 0.5e-3);
+    for (int chunk = 0; chunk < 4; ++chunk) {
+      cudaEventRecord(e0);
+      for (int it = 0; it < reps / 4; ++it) walk<<<tiles, 128>>>(it & 1 ? b : a, it & 1 ? a : b, 128L, pitch, G, 4);
+      cudaEventRecord(e1);
+      cudaEventSynchronize(e1);
+      float ms;
+      cudaEventElapsedTime(&ms, e0, e1);
+      printf("sustained row-major depth 4, quarter %d: %.3f ms/launch  %.0f GB/s (read+write)\n", chunk, ms / (reps / 4),
+             2.0 * 8 * pitch * G / (ms / (reps / 4) * 1e-3) / 1e9);
+    }
+  }
   printf("status %s\n", cudaGetErrorString(cudaGetLastError()));
   return 0;
 }

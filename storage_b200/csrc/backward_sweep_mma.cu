@@ -37,6 +37,12 @@
 #ifndef LSMC_MMA_MIN_CTAS
 #define LSMC_MMA_MIN_CTAS 3
 #endif
+#ifndef LSMC_MMA_WINNER_ONLY
+#define LSMC_MMA_WINNER_ONLY 1  // 0: form the carried value for all three decisions and select the value (round 2's first form)
+#endif
+#ifndef LSMC_MMA_MEMONLY
+#define LSMC_MMA_MEMONLY 0  // diagnostic build only (profiles/ab_library.sh): the kernel without its mma work; results are wrong
+#endif
 
 namespace lsmc {
 
@@ -246,10 +252,44 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
       double t[3][2];
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
+#if LSMC_MMA_MEMONLY  // diagnostic build: the kernel's data movement without its tensor work (results are wrong)
+        t[d][0] = sc[d].offset + af[d][0] * qb[j][0], t[d][1] = sc[d].offset_again + af[d][KSTEPS - 1] * qb[j][KSTEPS - 1];
+#else
         dmma_m8n8k4_to(t[d][0], t[d][1], af[d][0], qb[j][0], sc[d].offset, sc[d].offset_again);
 #pragma unroll
         for (int s = 1; s < KSTEPS; ++s) dmma_m8n8k4(t[d][0], t[d][1], af[d][s], qb[j][s]);
+#endif
       }
+#if LSMC_MMA_WINNER_ONLY
+      // first maximum wins (SH.cs:206-221); the value carried is formed for the winning decision only: immediate cash flow +
+      // realised continuation value (LSV.cs:296-302, 330-335), the weighted average of the two rows of V_{p+1} the decision
+      // lands between (an exact grid hit has lower == upper and weights (1, 0): the row itself).  Selecting the winner's
+      // scalars and row offsets costs ALU selects but a third of the FP64 operations and of the shared-memory wavefronts of
+      // forming the value for all three decisions.
+      double2 v;
+      {
+        const bool a1 = t[1][0] > t[0][0];
+        const double b1 = a1 ? t[1][0] : t[0][0];
+        const bool a2 = t[2][0] > b1;
+        auto pick = [&](auto x0, auto x1, auto x2) { return a2 ? x2 : (a1 ? x1 : x0); };
+        const double lo = *reinterpret_cast<const double *>(my_rows + pick(rw[0].x, rw[1].x, rw[2].x) + j * 64);
+        const double up = *reinterpret_cast<const double *>(my_rows + pick(rw[0].y, rw[1].y, rw[2].y) + j * 64);
+        v.x = __fma_rn(price[j].x, pick(sc[0].price_coef, sc[1].price_coef, sc[2].price_coef),
+                       __fma_rn(up, pick(sc[0].upper_w, sc[1].upper_w, sc[2].upper_w),
+                                __fma_rn(lo, pick(sc[0].lower_w, sc[1].lower_w, sc[2].lower_w), pick(sc[0].offset, sc[1].offset, sc[2].offset))));
+      }
+      {
+        const bool a1 = t[1][1] > t[0][1];
+        const double b1 = a1 ? t[1][1] : t[0][1];
+        const bool a2 = t[2][1] > b1;
+        auto pick = [&](auto x0, auto x1, auto x2) { return a2 ? x2 : (a1 ? x1 : x0); };
+        const double lo = *reinterpret_cast<const double *>(my_rows + pick(rw[0].x, rw[1].x, rw[2].x) + j * 64 + 8);
+        const double up = *reinterpret_cast<const double *>(my_rows + pick(rw[0].y, rw[1].y, rw[2].y) + j * 64 + 8);
+        v.y = __fma_rn(price[j].y, pick(sc[0].price_coef, sc[1].price_coef, sc[2].price_coef),
+                       __fma_rn(up, pick(sc[0].upper_w, sc[1].upper_w, sc[2].upper_w),
+                                __fma_rn(lo, pick(sc[0].lower_w, sc[1].lower_w, sc[2].lower_w), pick(sc[0].offset, sc[1].offset, sc[2].offset))));
+      }
+#else
       // value carried for a decision: immediate cash flow + realised continuation value (LSV.cs:296-302, 330-335), the weighted
       // average of the two rows of V_{p+1}; an exact grid hit has lower == upper and weights (1, 0): the row itself
       double2 w[3];
@@ -273,12 +313,17 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
           v.y = w[d].y;
         }
       }
+#endif
       if (store_g && own0 + 8 * j < a.N) *reinterpret_cast<double2 *>(vout + j * 64) = v;
       if (a.accumulate) {
 #pragma unroll
         for (int mb = 0; mb < MB; ++mb) {
+#if LSMC_MMA_MEMONLY
+          racc[mb].x += qp[j][mb].x * v.x, racc[mb].y += qp[j][mb].y * v.y;
+#else
           dmma_m8n8k4(racc[mb].x, racc[mb].y, qp[j][mb].x, v.x);
           dmma_m8n8k4(racc[mb].x, racc[mb].y, qp[j][mb].y, v.y);
+#endif
         }
       }
     }
