@@ -52,7 +52,7 @@ constexpr int kMmaThreads = 128;
 constexpr int kMmaWarps = kMmaThreads / 32;
 constexpr int kMmaBlockG = 8;                     // grid points per block = m of the m8n8k4 tile
 constexpr int kMmaGroups = 4;                     // 8-path groups per warp
-constexpr int kMmaGens = kMmaLookAhead + 1;       // generations (rows + record of one block) in flight or in use
+constexpr int kMmaGens = kMmaLookAhead + 1 + kMmaSlack;  // generations (rows + record of one block) in flight, in use or not yet released
 constexpr int kMmaRowBytes = kSweepTilePaths * 8;
 #ifndef LSMC_MMA_ACC_LAG
 #define LSMC_MMA_ACC_LAG 2
@@ -139,9 +139,9 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
   // is older than that kernel) and the per-path operand loads below overlap its tail — its last CTA folds the records alone
   // while the rest of the GPU would idle; only the records must wait for it.  Launched without the attribute the wait is a no-op.
   if (warp == 0) {
-    for (int j = 0; j < min(kMmaGens, nblocks); ++j) issue_rows(j);
+    for (int j = 0; j < min(kMmaLookAhead + 1, nblocks); ++j) issue_rows(j);
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    for (int j = 0; j < min(kMmaGens, nblocks); ++j) issue_record(j);
+    for (int j = 0; j < min(kMmaLookAhead + 1, nblocks); ++j) issue_record(j);
   }
 
   // ---- per-path operands, loaded once
@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     // warp may spin here (6.6 % of the kernel's stall samples), but it is the warp that is ahead: issuing after its own block
     // instead, with one more block of look-ahead, was measured 5-7 % slower.
     if (b > 0 && b + kMmaLookAhead < nblocks && warp == (b & 3)) {
-      mbar_wait(&s_eval[(b - 1) % kMmaGens], ((b - 1) / kMmaGens) & 1);
+      if (b - 1 - kMmaSlack >= 0) mbar_wait(&s_eval[(b - 1 - kMmaSlack) % kMmaGens], ((b - 1 - kMmaSlack) / kMmaGens) & 1);
       issue_rows(b + kMmaLookAhead);
       issue_record(b + kMmaLookAhead);
     }

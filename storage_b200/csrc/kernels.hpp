@@ -136,6 +136,12 @@ void launch_backward_sweep(const BackwardStepArgs &a, int gsplit, int64_t num_ti
 #define LSMC_MMA_LOOKAHEAD 2
 #endif
 constexpr int kMmaLookAhead = LSMC_MMA_LOOKAHEAD;  // generations of rows requested ahead of the block being evaluated
+#ifndef LSMC_MMA_SLACK
+#define LSMC_MMA_SLACK 1
+#endif
+// Generations kept beyond the look-ahead: the slot generation b + look-ahead goes into was last read by block b - 1 - slack,
+// so with slack the issuing warp does not have to wait for the slowest warp of the block just before its own.
+constexpr int kMmaSlack = LSMC_MMA_SLACK;
 constexpr int kMmaRowPitchBytes = kSweepTilePaths * 8 + 64;  // consecutive ring rows start in opposite halves of the 32 banks
 size_t mma_block_record_bytes(int K);
 size_t backward_sweep_mma_smem_bytes(int K, int ring_rows, int blocks_per_cta);

@@ -447,7 +447,9 @@ void build_device_tables(lsmc_handle *h) {
         int sweep_need = 0;
         for (int j = 0; j < groups; ++j) {
           if (j + 1 < groups && lo[j + 1] < lo[j]) sweep_ok = false;
-          sweep_need = std::max(sweep_need, hic[std::min(j + look_ahead, groups - 1)] - lo[j] + 1);
+          // (the FP64-mma kernel may still be reading block j - kMmaSlack when it requests the rows of block j + look_ahead)
+          const int oldest = h->use_mma ? std::max(j - kMmaSlack, 0) : j;
+          sweep_need = std::max(sweep_need, hic[std::min(j + look_ahead, groups - 1)] - lo[oldest] + 1);
         }
         if (sweep_need > kMaxSweepRing) sweep_ok = false;
         const int R = sweep_ok ? std::max(sweep_need, 2) : 0;
