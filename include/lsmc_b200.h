@@ -271,8 +271,8 @@ lsmc_status lsmc_simulate(lsmc_handle *h, int which, const lsmc_multi_factor_par
  * is rejected with LSMC_ERR_ARGUMENT — and occupies about 1.3 MB on every GPU that has the library loaded, until exit.
  * All calls share it and it keeps the previous call's rows (each call rewrites every row it reads, so nothing needs
  * clearing): calls whose GPU work overlaps, on different streams or from different host threads, corrupt each other's
- * table and must be serialised by the caller.  The first call on a device looks up the array's device address; make that
- * first call before starting any stream capture.  The kernel runs on `cuda_stream` (a cudaStream_t, NULL = default
+ * table and must be serialised by the caller.  The first call on a device looks up the array's device address (once per
+ * device, kept for later calls).  The kernel runs on `cuda_stream` (a cudaStream_t, NULL = default
  * stream); the call waits for it (it synchronises that stream) and returns after it has finished.  `device` is made current
  * for the duration of the call and the caller's current device is put back before it returns.  Errors: message via
  * lsmc_last_error(NULL). */
