@@ -1038,11 +1038,6 @@ void launch_for_k(int which, const void *args, dim3 grid, dim3 block, size_t sme
         break;
       }
       ensure_dynamic_smem<backward_step_kernel<KP, 0, false>>(smem);
-      {
-        static int carve = -2;
-        if (carve == -2) { const char *e = getenv("LSMC_CARVEOUT"); carve = e ? atoi(e) : -1; }
-        if (carve >= 0) cudaFuncSetAttribute(backward_step_kernel<KP, 0, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-      }
       backward_step_kernel<KP, 0, false><<<grid, block, smem, stream>>>(*static_cast<const BackwardStepArgs *>(args));
       break;
     case 4:
