@@ -213,3 +213,91 @@ def test_forced_inject_and_withdraw_npv_almost_equals_trivial_intrinsic_calc(): 
         expected += fwd[d] * withdraw_rate * (1 - withdraw_consumed) * df(settle_rule(d)) - withdraw_cost * withdraw_rate * df(d + 4)
     assert abs(results.Npv - expected) / abs(expected) <= 0.03
     assert np.isfinite(results.ValuationSimStandardError)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Trigger prices and returned simulation data on the reference's own fixture (LsmcStorageValuationTest.cs:180-192, 1131-1290)
+# ---------------------------------------------------------------------------------------------------------------------
+def reference_params(storage, num_sims, flags=None, inventory=5_685.0):
+    val_date, end = Day(2019, 8, 29), Day(2020, 4, 1)  # :126-192
+    b = LsmcValuationParameters.Builder()
+    b.CurrentPeriod = val_date
+    b.Inventory = inventory
+    b.ForwardCurve = {d: 53.5 + math.sin(2.0 * math.pi / 365.0 * d.OffsetFrom(val_date)) * 24.6 for d in val_date.EnumerateTo(end)}
+    b.Storage = storage
+    b.SettleDateRule = lambda d: Month(d.Start.year, d.Start.month).Offset(1).First() + 19
+    b.DiscountFactors = StorageHelper.CreateAct65ContCompDiscounter(0.055)
+    b.GridCalc = FixedSpacingStateSpaceGridCalc.CreateForFixedNumberOfPointsOnGlobalInventoryRange(storage, 100)
+    b.BasisFunctions = ONE_FACTOR_BASIS
+    if flags is not None:
+        b.SimulationDataReturned = flags
+    b.SimulateWithMultiFactorModelAndMersenneTwister(MultiFactorParameters.For1Factor(12.5, 0.95), num_sims, 11)
+    return b.Build()
+
+
+def test_withdraw_trigger_price_higher_than_inject_trigger_price():  # :1212-1221 (500 simulations, :180)
+    res = LsmcStorageValuation().Calculate(reference_params(reference_storage("simple"), 500))
+    both = [t for t in res.TriggerPrices.values() if t.HasWithdrawPrice and t.HasInjectPrice]
+    assert len(both) > 100
+    for t in both:
+        assert t.MaxWithdrawTriggerPrice > t.MaxInjectTriggerPrice
+
+
+def test_trigger_volumes_consistent_with_max_inject_withdraw_rate():  # :1255-1290
+    res = LsmcStorageValuation().Calculate(reference_params(reference_storage("simple"), 500))
+    max_withdrawal_rate, max_injection_rate, max_inventory, min_inventory = 850.0, 625.0, 52_500.0, 0.0
+    assert len(res.TriggerPrices) > 200
+    for day, t in res.TriggerPrices.items():
+        profile = res.TriggerPriceVolumeProfiles[day]
+        expected_inventory = res.ExpectedStorageProfile[day].Inventory
+        if t.HasInjectPrice:
+            expected = min(max_injection_rate, max_inventory - expected_inventory)
+            assert t.MaxInjectVolume == pytest.approx(expected, rel=1e-12, abs=1e-9)
+            assert max(v for v, _ in profile.InjectTriggerPrices) == pytest.approx(expected, rel=1e-12, abs=1e-9)
+        else:
+            assert len(profile.InjectTriggerPrices) == 0
+        if t.HasWithdrawPrice:
+            expected = min(max_withdrawal_rate, expected_inventory - min_inventory)
+            assert -t.MaxWithdrawVolume == pytest.approx(expected, rel=1e-12, abs=1e-9)
+            assert -min(v for v, _ in profile.WithdrawTriggerPrices) == pytest.approx(expected, rel=1e-12, abs=1e-9)
+        else:
+            assert len(profile.WithdrawTriggerPrices) == 0
+
+
+def test_no_withdraw_trigger_price_when_empty_and_no_inject_trigger_price_when_full():  # :1223-1253
+    empty = LsmcStorageValuation().Calculate(reference_params(reference_storage("simple"), 500, inventory=0.0))
+    first = empty.TriggerPrices[min(empty.TriggerPrices)]
+    assert not first.HasWithdrawPrice and first.MaxWithdrawVolume is None and first.MaxWithdrawTriggerPrice is None
+    assert len(empty.TriggerPriceVolumeProfiles[min(empty.TriggerPriceVolumeProfiles)].WithdrawTriggerPrices) == 0
+    full = LsmcStorageValuation().Calculate(reference_params(reference_storage("simple"), 500, inventory=52_500.0))
+    first = full.TriggerPrices[min(full.TriggerPrices)]
+    assert not first.HasInjectPrice and first.MaxInjectVolume is None and first.MaxInjectTriggerPrice is None
+    assert len(full.TriggerPriceVolumeProfiles[min(full.TriggerPriceVolumeProfiles)].InjectTriggerPrices) == 0
+
+
+PANELS = ("RegressionSpotPriceSim", "ValuationSpotPriceSim", "InventoryBySim", "InjectWithdrawVolumeBySim", "CmdtyConsumedBySim",
+          "InventoryLossBySim", "NetVolumeBySim", "PvByPeriodAndSim")
+
+
+def test_simulation_data_returned_sizes():  # :1131-1192 (20 simulations)
+    from storage_b200 import SimulationDataReturned as S
+    num_sims = 20
+    storage = reference_storage("simple")
+    everything = LsmcStorageValuation().Calculate(reference_params(storage, num_sims, S.All))
+    for name in PANELS:
+        assert getattr(everything, name).shape[1] == num_sims, name
+    assert len(everything.RegressionMarkovFactors) == 1 and len(everything.ValuationMarkovFactors) == 1
+    for panel in everything.RegressionMarkovFactors + everything.ValuationMarkovFactors:
+        assert panel.shape[1] == num_sims
+    nothing = LsmcStorageValuation().Calculate(reference_params(storage, num_sims, S.Nothing))
+    for name in PANELS:
+        assert getattr(nothing, name).size == 0, name
+    assert all(p.size == 0 for p in nothing.RegressionMarkovFactors + nothing.ValuationMarkovFactors)
+    some = LsmcStorageValuation().Calculate(reference_params(storage, num_sims, S.Inventory | S.Pv | S.FactorsForValuation))
+    for name in PANELS:
+        expected_cols = num_sims if name in ("InventoryBySim", "PvByPeriodAndSim") else 0
+        got = getattr(some, name)
+        assert (got.shape[1] if got.size else 0) == expected_cols, name
+    assert all(p.size == 0 for p in some.RegressionMarkovFactors)
+    assert len(some.ValuationMarkovFactors) == 1 and some.ValuationMarkovFactors[0].shape[1] == num_sims
+    assert some.Npv == everything.Npv == nothing.Npv
