@@ -48,10 +48,13 @@ namespace lsmc {
 
 namespace {
 
-constexpr int kMmaThreads = 128;
-constexpr int kMmaWarps = kMmaThreads / 32;
+#ifndef LSMC_MMA_GROUPS
+#define LSMC_MMA_GROUPS 4
+#endif
+constexpr int kMmaGroups = LSMC_MMA_GROUPS;       // 8-path groups per warp
+constexpr int kMmaWarps = kSweepTilePaths / (8 * kMmaGroups);
+constexpr int kMmaThreads = 32 * kMmaWarps;
 constexpr int kMmaBlockG = 8;                     // grid points per block = m of the m8n8k4 tile
-constexpr int kMmaGroups = 4;                     // 8-path groups per warp
 constexpr int kMmaGens = kMmaLookAhead + 1 + kMmaSlack;  // generations (rows + record of one block) in flight, in use or not yet released
 constexpr int kMmaRowBytes = kSweepTilePaths * 8;
 #ifndef LSMC_MMA_ACC_LAG
@@ -60,7 +63,7 @@ constexpr int kMmaRowBytes = kSweepTilePaths * 8;
 constexpr int kAccLag = LSMC_MMA_ACC_LAG;         // blocks between a warp writing its regression-sum slice and the slices being combined
 constexpr int kAccBufs = 2 * kAccLag;             // slice buffers: a warp may be kAccLag blocks ahead of the slowest one
 constexpr int kAccBars = kAccLag < 2 ? 2 : kAccLag;  // hand-off barriers: block b + kAccLag must not share one with a block still open
-static_assert(kMmaWarps * kMmaGroups * 8 == kSweepTilePaths, "4 warps x 4 groups x 8 paths = one 128-path tile");
+static_assert(kMmaWarps * kMmaGroups * 8 == kSweepTilePaths && (kMmaWarps & (kMmaWarps - 1)) == 0, "warps x groups x 8 paths = one 128-path tile");
 
 template <int KSTEPS, int MB>
 __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep_mma_kernel(BackwardStepArgs a) {
@@ -148,7 +151,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
   // Columns in [N, pitch) are padding of the row buffers: zero in the basis rows and in the terminal values, hence finite in
   // every row.  Lanes that own them compute on them like on any other column; a pair that straddles N is stored (and stays
   // finite), a pair entirely beyond N is not.  Padding never reaches the regression sums: the q_prev fragments are zero there.
-  const int64_t warp_path0 = tile * kSweepTilePaths + 32 * warp;
+  const int64_t warp_path0 = tile * kSweepTilePaths + 8 * kMmaGroups * warp;
   // B fragments of qx = (basis row, spot price): lane (r, c) supplies coefficient 4 s + c of path 8 j + r of the warp
   double qb[kMmaGroups][KSTEPS];
 #pragma unroll
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
   }
 
   const int last = glimit - 1;
-  const uint32_t own_col_bytes = (uint32_t)(32 * warp + 2 * c) * 8u;   // the lane's first pair inside a ring row
+  const uint32_t own_col_bytes = (uint32_t)(8 * kMmaGroups * warp + 2 * c) * 8u;   // the lane's first pair inside a ring row
   char *vout = reinterpret_cast<char *>(a.v_this + (size_t)(gbeg + r) * a.pitch + own0);
   double *my_acc = s_acc + (size_t)warp * ACC * kMmaBlockG + r * kMmaBlockG + 2 * c;  // C fragment: [k][g], two adjacent g per lane
 
@@ -224,7 +227,7 @@ __global__ void __launch_bounds__(kMmaThreads, LSMC_MMA_MIN_CTAS) backward_sweep
     // generation b + look-ahead overwrites ring slots and the record slot that block b - 1 was the last to read.  The issuing
     // warp may spin here (6.6 % of the kernel's stall samples), but it is the warp that is ahead: issuing after its own block
     // instead, with one more block of look-ahead, was measured 5-7 % slower.
-    if (b > 0 && b + kMmaLookAhead < nblocks && warp == (b & 3)) {
+    if (b > 0 && b + kMmaLookAhead < nblocks && warp == (b & (kMmaWarps - 1))) {
       if (b - 1 - kMmaSlack >= 0) mbar_wait(&s_eval[(b - 1 - kMmaSlack) % kMmaGens], ((b - 1 - kMmaSlack) / kMmaGens) & 1);
       issue_rows(b + kMmaLookAhead);
       issue_record(b + kMmaLookAhead);
